@@ -1,0 +1,135 @@
+/*
+ * wgpt.h -- C ABI of libwgpt.so: the B200 (sm_100a CUDA) replacement for the reference's
+ * compute-shader path-tracing hot path.
+ *
+ * The boundary mirrors what /root/reference/renderer.js does to WebGPU:
+ *   - bind group 0 of `computeFrameBuffer`, bindings 0,1,2,3,5,6,7,8,9
+ *     (renderer.js:109-123, shaders/header.wgsl:15-23)            -> wgpt_write_buffer
+ *   - queue.writeBuffer(uniforms) + dispatchWorkgroups per frame
+ *     (renderer.js:182-188, webgpu-utils.js:125-134)              -> wgpt_dispatch / wgpt_render
+ *   - the present pass `fs` reading binding 3
+ *     (renderer.js:130-136,191, shaders/fragment.js:22-36)        -> wgpt_present
+ * Plain pointers and sizes only.  Every call returns 0 on success or a negative WGPT_E_* code;
+ * wgpt_last_error() gives the message.  One context = one CUDA device = one caller thread at a
+ * time.  Calls enqueue on the context's stream and return; read_buffer/present/counters/
+ * primary_hits/sample_radiance/trace_rays synchronise.  There is NO CPU fallback: without a
+ * CUDA device wgpt_create fails with WGPT_E_CUDA.
+ */
+#ifndef WGPT_H
+#define WGPT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WGPT_VERSION 1
+
+/* error codes */
+#define WGPT_OK            0
+#define WGPT_E_INVALID    -1   /* bad argument / binding / size not a multiple of the stride */
+#define WGPT_E_CUDA       -2   /* CUDA runtime error (or no device) */
+#define WGPT_E_STATE      -3   /* call order: scene or uniforms missing */
+#define WGPT_E_NOMEM      -4
+
+/* binding numbers of shaders/header.wgsl:15-23 and their element strides in bytes */
+#define WGPT_BINDING_UNIFORMS    0   /* 80 B  Uniforms       header.wgsl:41-46  */
+#define WGPT_BINDING_SPHERES     1   /* 32 B  Sphere         header.wgsl:68-74  */
+#define WGPT_BINDING_QUADS       2   /* 80 B  Quad           header.wgsl:76-86  */
+#define WGPT_BINDING_FRAMEBUFFER 3   /* 16 B  vec4f / pixel  header.wgsl:18     */
+#define WGPT_BINDING_TRIANGLES   5   /* 96 B  Triangle       header.wgsl:88-98  */
+#define WGPT_BINDING_MESHES      6   /* 16 B  Mesh (4 x i32) header.wgsl:100-105 */
+#define WGPT_BINDING_TRANSFORMS  7   /* 128 B modelTransform header.wgsl:63-66  */
+#define WGPT_BINDING_MATERIALS   8   /* 64 B  Material       header.wgsl:53-61  */
+#define WGPT_BINDING_BVH         9   /* 48 B  AABB node      header.wgsl:107-117 */
+
+/* integrator implementations */
+#define WGPT_MODE_EXACT 0   /* one thread per pixel, the reference's binary BVH and operation order;
+                               bit-identical to the oracle (pinned IEEE arithmetic, no FMA)          */
+#define WGPT_MODE_FAST  1   /* persistent-thread wavefront over SoA ray queues on the 8-wide quantised
+                               BVH; same RNG stream and intersection arithmetic, fast shading math   */
+
+/* The WGSL compile-time constants (shaders/header.wgsl:9-13) are run-time parameters here. */
+typedef struct wgpt_config {
+    uint32_t struct_size;          /* sizeof(wgpt_config), for forward compatibility */
+    int32_t  width, height;        /* canvas size; uniforms.screenDims must match */
+    int32_t  device;               /* CUDA device ordinal */
+    int32_t  mode;                 /* WGPT_MODE_* */
+    int32_t  num_samples;          /* NUM_SAMPLES          (reference HEAD: 1)   */
+    int32_t  max_bounces;          /* MAX_BOUNCES          (100)                 */
+    int32_t  stratify;             /* STRATIFY             (false)               */
+    int32_t  importance_sampling;  /* IMPORTANCE_SAMPLING  (false)               */
+    int32_t  stack_size;           /* STACK_SIZE           (20), <= 64           */
+    /* multi-GPU sharding; world = 1 renders everything.
+     * Tile split: rows are grouped in blocks of `tile_rows`; this context renders block b iff
+     * b % tile_world == tile_rank.  Pixels outside the shard are never written (they stay 0), so
+     * a sum-reduce of the shards' framebuffers reproduces the single-GPU buffer bit for bit.
+     * Frame-strata split: wgpt_render renders frame f iff f % strata_world == strata_rank.   */
+    int32_t  tile_rank, tile_world, tile_rows;
+    int32_t  strata_rank, strata_world;
+} wgpt_config;
+
+typedef struct wgpt_ctx wgpt_ctx;
+
+/* counters reported by wgpt_counters (same order as the oracle's) */
+typedef struct wgpt_counter_block {
+    uint64_t rays;          /* closest-hit queries (hitScene calls, hitRay.wgsl:1)      */
+    uint64_t node_visits;   /* hit_aabb calls on the reference's binary BVH (exact mode)
+                               or wide-node visits (fast mode)                          */
+    uint64_t tri_tests;     /* hit_triangle calls                                       */
+    uint64_t sphere_tests, quad_tests, rng_draws, samples, stack_aborts;
+} wgpt_counter_block;
+
+void wgpt_default_config(wgpt_config* cfg);
+int  wgpt_create(const wgpt_config* cfg, wgpt_ctx** out);
+void wgpt_destroy(wgpt_ctx* ctx);
+const char* wgpt_last_error(const wgpt_ctx* ctx);     /* ctx may be NULL: last create error */
+
+/* createBuffer + queue.writeBuffer (webgpu-utils.js:15-55): copies `bytes` from host memory at
+ * call time; element count = bytes / stride (arrayLength(), main.wgsl:10-14).  Writing binding
+ * 5 or 9 invalidates the derived wide BVH (rebuilt on the next dispatch in fast mode). */
+int wgpt_write_buffer(wgpt_ctx* ctx, int binding, const void* data, size_t bytes);
+/* device -> host copy of a binding (the reference never reads back; needed headless). */
+int wgpt_read_buffer(wgpt_ctx* ctx, int binding, void* out, size_t bytes);
+/* raw device pointer + size of a binding, for NCCL reductions on binding 3 by the host layer. */
+int wgpt_device_ptr(wgpt_ctx* ctx, int binding, void** dptr, size_t* bytes);
+
+/* One `computePass(...)`: one frame with the uniforms currently in binding 0
+ * (main.wgsl:1-28).  `workgroups` is what the caller would pass to dispatchWorkgroups
+ * (renderer.js:187-188: W*H/64 + 1); invocations with index >= W*H are masked. */
+int wgpt_dispatch(wgpt_ctx* ctx, uint32_t workgroups);
+/* Batched form of the renderAnimation loop (renderer.js:163-188) without camera motion:
+ * frames first_frame .. first_frame+n_frames-1, uniforms.frameNum advanced internally,
+ * resetBuffer = 0; leaves uniforms.frameNum at the last frame rendered. */
+int wgpt_render(wgpt_ctx* ctx, int first_frame, int n_frames);
+/* `fs` (fragment.js:22-36): rgba_out[4*i..] = (pow(aces(fb[i].xyz / frameNum), 1/2.2), 1);
+ * clears binding 3 when uniforms.resetBuffer == 1.  rgba_out: host, 4 floats per pixel;
+ * rgba8_out (optional, may be NULL): host, 4 bytes per pixel, round(c*255). */
+int wgpt_present(wgpt_ctx* ctx, float* rgba_out, uint8_t* rgba8_out);
+
+/* ---- parity hooks (no reference counterpart) ---- */
+/* Re-runs one dispatch with the current uniforms WITHOUT touching binding 3 and returns, per
+ * pixel, the first closest-hit query of the invocation: type 0 sphere / 1 quad / 2 triangle /
+ * -1 miss, index (sphere/quad index, Triangle.local_id), t; and pathTrace()'s radiance (3 f32). */
+int wgpt_probe(wgpt_ctx* ctx, float* radiance_out, int32_t* prim_type, int32_t* prim_index, float* prim_t);
+/* Closest hit of caller-supplied rays (6 f32 each: origin, dir); seeds[i] = RNG state on entry. */
+int wgpt_trace_rays(wgpt_ctx* ctx, int n, const float* rays, const uint32_t* seeds,
+                    int32_t* prim_type, int32_t* prim_index, float* prim_t);
+int wgpt_counters(wgpt_ctx* ctx, wgpt_counter_block* out, int reset);
+/* enable/disable counter collection (adds atomics to the kernels; off by default) */
+int wgpt_set_counters(wgpt_ctx* ctx, int enabled);
+
+/* ---- device-resident timing of the last wgpt_render/wgpt_dispatch (CUDA events on the
+ * context's stream): total milliseconds and number of kernel launches issued. ---- */
+int wgpt_last_timing(wgpt_ctx* ctx, float* ms, uint64_t* launches);
+int wgpt_synchronize(wgpt_ctx* ctx);
+
+/* pinned-math probe for tests: fn 0 sin, 1 cos, 2 acos, 3 log, 4 pow(x,y), evaluated ON THE GPU */
+int wgpt_pinned_math(wgpt_ctx* ctx, int fn, int n, const float* x, const float* y, float* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -32,42 +32,57 @@
 
 namespace wgpt_pm {
 
+/* multiply / add / subtract that can never be fused into an FMA: on the device the _rn
+ * intrinsics (ptxas never contracts them, whatever -fmad says); on the host plain operators,
+ * which the oracle's build pins with -ffp-contract=off. */
+#if defined(__CUDA_ARCH__)
+WGPT_HD double dm(double a, double b) { return __dmul_rn(a, b); }
+WGPT_HD double da(double a, double b) { return __dadd_rn(a, b); }
+WGPT_HD double ds(double a, double b) { return __dsub_rn(a, b); }
+#else
+WGPT_HD double dm(double a, double b) { return a * b; }
+WGPT_HD double da(double a, double b) { return a + b; }
+WGPT_HD double ds(double a, double b) { return a - b; }
+#endif
+/* Horner step p*z + c */
+WGPT_HD double hs(double p, double z, double c) { return da(dm(p, z), c); }
+
 WGPT_HD int64_t d2bits(double d) { int64_t b; memcpy(&b, &d, 8); return b; }
 WGPT_HD double  bits2d(int64_t b) { double d; memcpy(&d, &b, 8); return d; }
 
 /* sin and cos of r, |r| <= pi/4 (Taylor, Horner in r*r; remainder < 5e-17). */
 WGPT_HD double ksin(double r) {
-    const double z = r * r;
+    const double z = dm(r, r);
     double p = 2.8114572543455206e-15;            /*  1/17! */
-    p = p * z + -7.6471637318198164e-13;          /* -1/15! */
-    p = p * z + 1.6059043836821613e-10;           /*  1/13! */
-    p = p * z + -2.5052108385441720e-08;          /* -1/11! */
-    p = p * z + 2.7557319223985893e-06;           /*  1/9!  */
-    p = p * z + -1.9841269841269841e-04;          /* -1/7!  */
-    p = p * z + 8.3333333333333332e-03;           /*  1/5!  */
-    p = p * z + -1.6666666666666666e-01;          /* -1/3!  */
-    return r + r * (z * p);
+    p = hs(p, z, -7.6471637318198164e-13);          /* -1/15! */
+    p = hs(p, z, 1.6059043836821613e-10);           /*  1/13! */
+    p = hs(p, z, -2.5052108385441720e-08);          /* -1/11! */
+    p = hs(p, z, 2.7557319223985893e-06);           /*  1/9!  */
+    p = hs(p, z, -1.9841269841269841e-04);          /* -1/7!  */
+    p = hs(p, z, 8.3333333333333332e-03);           /*  1/5!  */
+    p = hs(p, z, -1.6666666666666666e-01);          /* -1/3!  */
+    return da(r, dm(r, dm(z, p)));
 }
 WGPT_HD double kcos(double r) {
-    const double z = r * r;
+    const double z = dm(r, r);
     double p = 4.7794773323873853e-14;            /*  1/16! */
-    p = p * z + -1.1470745597729725e-11;          /* -1/14! */
-    p = p * z + 2.0876756987868100e-09;           /*  1/12! */
-    p = p * z + -2.7557319223985888e-07;          /* -1/10! */
-    p = p * z + 2.4801587301587302e-05;           /*  1/8!  */
-    p = p * z + -1.3888888888888889e-03;          /* -1/6!  */
-    p = p * z + 4.1666666666666664e-02;           /*  1/4!  */
-    p = p * z + -0.5;                             /* -1/2!  */
-    return 1.0 + z * p;
+    p = hs(p, z, -1.1470745597729725e-11);          /* -1/14! */
+    p = hs(p, z, 2.0876756987868100e-09);           /*  1/12! */
+    p = hs(p, z, -2.7557319223985888e-07);          /* -1/10! */
+    p = hs(p, z, 2.4801587301587302e-05);           /*  1/8!  */
+    p = hs(p, z, -1.3888888888888889e-03);          /* -1/6!  */
+    p = hs(p, z, 4.1666666666666664e-02);           /*  1/4!  */
+    p = hs(p, z, -0.5);                             /* -1/2!  */
+    return da(1.0, dm(z, p));
 }
 
 /* Two-part Cody-Waite reduction by pi/2 (k*PIO2_HI is exact for |k| < 2^20). */
 WGPT_HD double reduce_pio2(double x, int* quadrant) {
     const double PIO2_HI = 1.57079632673412561417e+00;   /* 0x3FF921FB54400000 */
     const double PIO2_LO = 6.07710050650619224932e-11;   /* 0x3DD0B4611A626331 */
-    const double k = rint(x * 6.36619772367581382433e-01);
+    const double k = rint(dm(x, 6.36619772367581382433e-01));
     *quadrant = (int)((long long)k & 3);
-    return (x - k * PIO2_HI) - k * PIO2_LO;
+    return ds(ds(x, dm(k, PIO2_HI)), dm(k, PIO2_LO));
 }
 
 WGPT_HD double sin_d(double x) {
@@ -81,19 +96,23 @@ WGPT_HD double cos_d(double x) {
 
 /* asin for |z| <= 0.5: series start + two Newton steps on sin (cos >= 0.866, well conditioned). */
 WGPT_HD double kasin(double z) {
-    const double z2 = z * z;
-    double t = z * (1.0 + z2 * (1.0 / 6.0 + z2 * (3.0 / 40.0 + z2 * (15.0 / 336.0))));
-    t = t - (ksin(t) - z) / kcos(t);
-    t = t - (ksin(t) - z) / kcos(t);
-    t = t - (ksin(t) - z) / kcos(t);
+    const double z2 = dm(z, z);
+    double p = 15.0 / 336.0;
+    p = hs(p, z2, 3.0 / 40.0);
+    p = hs(p, z2, 1.0 / 6.0);
+    p = hs(p, z2, 1.0);
+    double t = dm(z, p);
+    t = ds(t, ds(ksin(t), z) / kcos(t));
+    t = ds(t, ds(ksin(t), z) / kcos(t));
+    t = ds(t, ds(ksin(t), z) / kcos(t));
     return t;
 }
 WGPT_HD double acos_d(double x) {
     const double PI_D = 3.14159265358979311600e+00, PIO2_D = 1.57079632679489655800e+00;
     if (x != x || x > 1.0 || x < -1.0) return bits2d(0x7ff8000000000000LL);
-    if (x > 0.5)  return 2.0 * kasin(sqrt((1.0 - x) * 0.5));
-    if (x < -0.5) return PI_D - 2.0 * kasin(sqrt((1.0 + x) * 0.5));
-    return PIO2_D - kasin(x);
+    if (x > 0.5)  return dm(2.0, kasin(sqrt(dm(ds(1.0, x), 0.5))));
+    if (x < -0.5) return ds(PI_D, dm(2.0, kasin(sqrt(dm(da(1.0, x), 0.5)))));
+    return ds(PIO2_D, kasin(x));
 }
 
 /* natural log of a positive finite normal double (floats widen to normal doubles). */
@@ -101,15 +120,16 @@ WGPT_HD double log_pos(double d) {
     int64_t b = d2bits(d);
     int e = (int)((b >> 52) & 0x7ff) - 1023;
     double m = bits2d((b & 0x000fffffffffffffLL) | 0x3ff0000000000000LL);
-    if (m > 1.41421356237309514547) { m = m * 0.5; e += 1; }
-    const double s = (m - 1.0) / (m + 1.0), w = s * s;
+    if (m > 1.41421356237309514547) { m = dm(m, 0.5); e += 1; }
+    const double s = ds(m, 1.0) / da(m, 1.0), w = dm(s, s);
     double p = 1.0 / 23.0;
-    p = p * w + 1.0 / 21.0;  p = p * w + 1.0 / 19.0;  p = p * w + 1.0 / 17.0;
-    p = p * w + 1.0 / 15.0;  p = p * w + 1.0 / 13.0;  p = p * w + 1.0 / 11.0;
-    p = p * w + 1.0 / 9.0;   p = p * w + 1.0 / 7.0;   p = p * w + 1.0 / 5.0;
-    p = p * w + 1.0 / 3.0;
-    const double logm = 2.0 * s + 2.0 * s * (w * p);
-    return (double)e * 6.93147180559945286227e-01 + logm;
+    p = hs(p, w, 1.0 / 21.0);  p = hs(p, w, 1.0 / 19.0);  p = hs(p, w, 1.0 / 17.0);
+    p = hs(p, w, 1.0 / 15.0);  p = hs(p, w, 1.0 / 13.0);  p = hs(p, w, 1.0 / 11.0);
+    p = hs(p, w, 1.0 / 9.0);   p = hs(p, w, 1.0 / 7.0);   p = hs(p, w, 1.0 / 5.0);
+    p = hs(p, w, 1.0 / 3.0);
+    const double s2 = dm(2.0, s);
+    const double logm = da(s2, dm(s2, dm(w, p)));
+    return da(dm((double)e, 6.93147180559945286227e-01), logm);
 }
 WGPT_HD double log_d(double x) {
     if (x != x || x < 0.0) return bits2d(0x7ff8000000000000LL);
@@ -124,23 +144,23 @@ WGPT_HD double exp_d(double t) {
     if (t < -700.0) return 0.0;
     const double LN2_HI = 6.93147180369123816490e-01;    /* 0x3fe62e42fee00000 */
     const double LN2_LO = 1.90821492927058770002e-10;    /* 0x3dea39ef35793c76 */
-    const double k = rint(t * 1.44269504088896338700e+00);
-    const double r = (t - k * LN2_HI) - k * LN2_LO;
+    const double k = rint(dm(t, 1.44269504088896338700e+00));
+    const double r = ds(ds(t, dm(k, LN2_HI)), dm(k, LN2_LO));
     double p = 1.6059043836821613e-10;            /* 1/13! */
-    p = p * r + 2.0876756987868100e-09;           /* 1/12! */
-    p = p * r + 2.5052108385441720e-08;           /* 1/11! */
-    p = p * r + 2.7557319223985888e-07;           /* 1/10! */
-    p = p * r + 2.7557319223985893e-06;           /* 1/9!  */
-    p = p * r + 2.4801587301587302e-05;           /* 1/8!  */
-    p = p * r + 1.9841269841269841e-04;           /* 1/7!  */
-    p = p * r + 1.3888888888888889e-03;           /* 1/6!  */
-    p = p * r + 8.3333333333333332e-03;           /* 1/5!  */
-    p = p * r + 4.1666666666666664e-02;           /* 1/4!  */
-    p = p * r + 1.6666666666666666e-01;           /* 1/3!  */
-    p = p * r + 0.5;
-    p = p * r + 1.0;
-    p = p * r + 1.0;
-    return p * bits2d(((int64_t)k + 1023) << 52);
+    p = hs(p, r, 2.0876756987868100e-09);           /* 1/12! */
+    p = hs(p, r, 2.5052108385441720e-08);           /* 1/11! */
+    p = hs(p, r, 2.7557319223985888e-07);           /* 1/10! */
+    p = hs(p, r, 2.7557319223985893e-06);           /* 1/9!  */
+    p = hs(p, r, 2.4801587301587302e-05);           /* 1/8!  */
+    p = hs(p, r, 1.9841269841269841e-04);           /* 1/7!  */
+    p = hs(p, r, 1.3888888888888889e-03);           /* 1/6!  */
+    p = hs(p, r, 8.3333333333333332e-03);           /* 1/5!  */
+    p = hs(p, r, 4.1666666666666664e-02);           /* 1/4!  */
+    p = hs(p, r, 1.6666666666666666e-01);           /* 1/3!  */
+    p = hs(p, r, 0.5);
+    p = hs(p, r, 1.0);
+    p = hs(p, r, 1.0);
+    return dm(p, bits2d(((int64_t)k + 1023) << 52));
 }
 
 /* ---- the float entry points the shader restatements call ---- */
@@ -154,7 +174,7 @@ WGPT_HD float powf_(float x, float y) {
     if (y == 0.0f || x == 1.0f) return 1.0f;
     if (x < 0.0f) return (float)bits2d(0x7ff8000000000000LL);
     if (x == 0.0f) return y > 0.0f ? 0.0f : (float)bits2d(0x7ff0000000000000LL);
-    return (float)exp_d((double)y * log_d((double)x));
+    return (float)exp_d(dm((double)y, log_d((double)x)));
 }
 
 }  /* namespace wgpt_pm */

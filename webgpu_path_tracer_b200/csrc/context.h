@@ -1,0 +1,50 @@
+// context.h -- the state behind a wgpt_ctx: device copies of the bind-group buffers, the
+// stream, scratch for the parity hooks and (fast mode) the derived wide BVH + wavefront pool.
+#pragma once
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../../include/wgpt.h"
+#include "scene.cuh"
+
+namespace wg { struct FastState; }
+
+struct wgpt_ctx {
+    wgpt_config cfg;
+    cudaStream_t stream = nullptr;
+    void* dbuf[10] = {nullptr};            // device copy of each binding (0 unused: uniforms travel by value)
+    size_t dbytes[10] = {0};
+    std::vector<unsigned char> hbuf[10];   // host mirrors of the small tables (lights lookup, validation)
+    wg::Uniforms uniforms;
+    bool have_uniforms = false;
+    wg::Quad lights;
+    bool lights_valid = false;
+    unsigned long long* d_counters = nullptr;
+    bool counters_on = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timing_valid = false;
+    uint64_t last_launches = 0;
+    uint32_t shard_pixels = 0;
+    // probe scratch
+    float* d_radiance = nullptr; int* d_ptype = nullptr; int* d_pindex = nullptr; float* d_pt = nullptr;
+    wg::FastState* fast = nullptr;         // wide BVH + wavefront pool (fast.cu)
+    bool wide_dirty = true;
+    // summary of the big device-only tables, gathered at upload time for validation
+    int tri_mesh_max = -1; bool tri_bad = false;
+    long long bvh_prim_end_max = 0; bool bvh_bad = false;
+    std::string err;
+};
+
+namespace wg {
+// assembles the by-value descriptor for a launch; pixel_limit = invocations dispatched
+DeviceScene make_device_scene(wgpt_ctx* c, uint32_t pixel_limit);
+int set_err(wgpt_ctx* c, int code, const std::string& msg);
+int cuda_err(wgpt_ctx* c, cudaError_t e, const char* what);
+int ready(wgpt_ctx* c);
+int validate_scene(wgpt_ctx* c);
+
+// fast.cu
+int fast_render(wgpt_ctx* c, int first_frame, int n_frames, int reset_first);
+int fast_trace_rays(wgpt_ctx* c, int n, const float* d_rays, const uint32_t* d_seeds, int* d_type, int* d_index, float* d_t);
+void fast_destroy(wgpt_ctx* c);
+}
