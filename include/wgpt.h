@@ -126,6 +126,16 @@ int wgpt_set_counters(wgpt_ctx* ctx, int enabled);
 int wgpt_last_timing(wgpt_ctx* ctx, float* ms, uint64_t* launches);
 int wgpt_synchronize(wgpt_ctx* ctx);
 
+/* fast-mode introspection: the derived wide BVH, the wavefront pool, and how many rays had to be
+ * re-traced with the reference-order binary walk (equal-distance triangles / stack overflow). */
+typedef struct wgpt_fast_stats {
+    uint32_t wide_nodes, wide_tris, wide_levels;   /* K2 output */
+    uint32_t pool_slots, ring_frames;              /* K3 pool capacity, frames in flight */
+    uint32_t fallback_rays, iterations;            /* of the last wgpt_render / wgpt_dispatch / wgpt_probe */
+    uint32_t trace_fallback_rays;                  /* of wgpt_trace_rays since creation */
+} wgpt_fast_stats;
+int wgpt_fast_statistics(wgpt_ctx* ctx, wgpt_fast_stats* out);
+
 /* pinned-math probe for tests: fn 0 sin, 1 cos, 2 acos, 3 log, 4 pow(x,y), evaluated ON THE GPU */
 int wgpt_pinned_math(wgpt_ctx* ctx, int fn, int n, const float* x, const float* y, float* out);
 

@@ -9,6 +9,7 @@
 #ifndef WGPT_ORACLE_OVEC_H
 #define WGPT_ORACLE_OVEC_H
 #include <math.h>
+#include <string.h>
 
 namespace orc {
 
@@ -31,10 +32,21 @@ static inline vec3 operator/(vec3 a, float s) { return V3(a.x / s, a.y / s, a.z 
 static inline vec3 operator/(float s, vec3 a) { return V3(s / a.x, s / a.y, s / a.z); }
 static inline vec3 operator-(vec3 a) { return V3(-a.x, -a.y, -a.z); }
 
-/* min/max with WGSL-compatible "return the non-NaN operand" behaviour, written out so the CPU
- * and the GPU evaluate the same decision tree. */
-static inline float fmin_(float a, float b) { return (a != a) ? b : ((b != b) ? a : (a < b ? a : b)); }
-static inline float fmax_(float a, float b) { return (a != a) ? b : ((b != b) ? a : (a > b ? a : b)); }
+/* min/max with the result BITS pinned (WGSL leaves NaN and signed-zero handling loose):
+ * NaN -> the other operand; min(-0,+0) = -0, max(-0,+0) = +0.  The CUDA side (csrc/pvec.cuh
+ * pmin/pmax) implements the same rule. */
+static inline float fmin_(float a, float b) {
+    if (a != a) return b;
+    if (b != b) return a;
+    if (a == b) { unsigned x, y; memcpy(&x, &a, 4); memcpy(&y, &b, 4); x |= y; float r; memcpy(&r, &x, 4); return r; }
+    return a < b ? a : b;
+}
+static inline float fmax_(float a, float b) {
+    if (a != a) return b;
+    if (b != b) return a;
+    if (a == b) { unsigned x, y; memcpy(&x, &a, 4); memcpy(&y, &b, 4); x &= y; float r; memcpy(&r, &x, 4); return r; }
+    return a > b ? a : b;
+}
 static inline vec3 vmin(vec3 a, vec3 b) { return V3(fmin_(a.x, b.x), fmin_(a.y, b.y), fmin_(a.z, b.z)); }
 static inline vec3 vmax(vec3 a, vec3 b) { return V3(fmax_(a.x, b.x), fmax_(a.y, b.y), fmax_(a.z, b.z)); }
 

@@ -7,12 +7,11 @@ import pytest
 from webgpu_path_tracer_b200 import PathTracer, MODE_EXACT
 from oracle.binding import Oracle
 from tests import scenes
+from tests.util import bits
 
 pytestmark = pytest.mark.gpu
 
 
-def bits(a):
-    return np.ascontiguousarray(a).view(np.uint32)
 
 
 def run_pair(scene, cam, W, H, frames, **cfg):

@@ -19,7 +19,7 @@ COUNTER_NAMES = ("rays", "node_visits", "tri_tests", "sphere_tests", "quad_tests
 EXPORTS = ("wgpt_default_config", "wgpt_create", "wgpt_destroy", "wgpt_last_error", "wgpt_write_buffer",
            "wgpt_read_buffer", "wgpt_device_ptr", "wgpt_dispatch", "wgpt_render", "wgpt_present", "wgpt_probe",
            "wgpt_trace_rays", "wgpt_counters", "wgpt_set_counters", "wgpt_last_timing", "wgpt_synchronize",
-           "wgpt_pinned_math")
+           "wgpt_pinned_math", "wgpt_fast_statistics")
 
 
 class WgptError(RuntimeError):
@@ -32,6 +32,11 @@ class Config(C.Structure):
                 ("importance_sampling", C.c_int32), ("stack_size", C.c_int32),
                 ("tile_rank", C.c_int32), ("tile_world", C.c_int32), ("tile_rows", C.c_int32),
                 ("strata_rank", C.c_int32), ("strata_world", C.c_int32)]
+
+
+class FastStats(C.Structure):
+    _fields_ = [(n, C.c_uint32) for n in ("wide_nodes", "wide_tris", "wide_levels", "pool_slots", "ring_frames",
+                                          "fallback_rays", "iterations", "trace_fallback_rays")]
 
 
 class CounterBlock(C.Structure):
@@ -72,6 +77,7 @@ def load_library(path=None):
     L.wgpt_last_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_uint64)]
     L.wgpt_synchronize.argtypes = [vp]
     L.wgpt_pinned_math.argtypes = [vp, i32, i32, vp, vp, vp]
+    L.wgpt_fast_statistics.argtypes = [vp, C.POINTER(FastStats)]
     if path is None:
         _lib = L
     return L
@@ -190,6 +196,11 @@ class PathTracer:
         blk = CounterBlock()
         self._ck(self.L.wgpt_counters(self.h, C.byref(blk), int(reset)), "wgpt_counters")
         return {n: int(getattr(blk, n)) for n in COUNTER_NAMES}
+
+    def fast_statistics(self):
+        st = FastStats()
+        self._ck(self.L.wgpt_fast_statistics(self.h, C.byref(st)), "wgpt_fast_statistics")
+        return {n: int(getattr(st, n)) for n, _ in FastStats._fields_}
 
     def pinned_math(self, fn, x, y=None):
         names = {"sin": 0, "cos": 1, "acos": 2, "log": 3, "pow": 4}

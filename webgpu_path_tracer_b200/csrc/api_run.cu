@@ -60,7 +60,7 @@ int wgpt_dispatch(wgpt_ctx* c, uint32_t workgroups) {
     const uint32_t limit = inv > 0xffffffffull ? 0xffffffffu : (uint32_t)inv;
     cudaEventRecord(c->ev0, c->stream);
     c->last_launches = 0;
-    if (c->cfg.mode == WGPT_MODE_FAST && limit >= (uint32_t)c->cfg.width * c->cfg.height) {
+    if (c->cfg.mode == WGPT_MODE_FAST && c->cfg.max_bounces >= 1 && limit >= (uint32_t)c->cfg.width * c->cfg.height) {
         rc = fast_render(c, (int)c->uniforms.frameNum, 1, c->uniforms.resetBuffer != 0.0f);
     } else {
         // (a partial dispatch -- fewer workgroups than pixels -- always takes the one-thread-per-pixel path)
@@ -82,7 +82,7 @@ int wgpt_render(wgpt_ctx* c, int first_frame, int n_frames) {
     c->uniforms.resetBuffer = 0.0f;
     cudaEventRecord(c->ev0, c->stream);
     c->last_launches = 0;
-    if (c->cfg.mode == WGPT_MODE_FAST) rc = fast_render(c, first_frame, n_frames, 0);
+    if (c->cfg.mode == WGPT_MODE_FAST && c->cfg.max_bounces >= 1) rc = fast_render(c, first_frame, n_frames, 0);
     else rc = exact_render(c, first_frame, n_frames, 0xffffffffu);
     if (n_frames > 0) c->uniforms.frameNum = (float)(first_frame + n_frames - 1);
     cudaEventRecord(c->ev1, c->stream);
@@ -116,6 +116,25 @@ int wgpt_probe(wgpt_ctx* c, float* radiance_out, int32_t* prim_type, int32_t* pr
     cudaMemsetAsync(c->d_ptype, 0xff, npix * 4, c->stream);
     cudaMemsetAsync(c->d_pindex, 0xff, npix * 4, c->stream);
     cudaMemsetAsync(c->d_pt, 0, npix * 4, c->stream);
+    if (c->cfg.mode == WGPT_MODE_FAST && c->cfg.max_bounces >= 1) {
+        // through the wavefront: render the frame into a scratch copy of binding 3 (reset semantics:
+        // the scratch then holds exactly this frame's per-pixel radiance), binding 3 itself untouched
+        HostScratch d_fb;
+        cudaError_t e = cudaMalloc(&d_fb.p, npix * 16);
+        if (e != cudaSuccess) return cuda_err(c, e, "probe");
+        cudaMemsetAsync(d_fb.p, 0, npix * 16, c->stream);
+        void* real_fb = c->dbuf[3];
+        c->dbuf[3] = d_fb.p;
+        rc = fast_render_probe(c, (int)c->uniforms.frameNum, 1, 1, c->d_ptype, c->d_pindex, c->d_pt);
+        c->dbuf[3] = real_fb;
+        if (rc) return rc;
+        launch_fb_to_rgb((const float4*)d_fb.p, c->d_radiance, (uint32_t)npix, c->stream);
+        if (radiance_out) cudaMemcpyAsync(radiance_out, c->d_radiance, npix * 12, cudaMemcpyDeviceToHost, c->stream);
+        if (prim_type) cudaMemcpyAsync(prim_type, c->d_ptype, npix * 4, cudaMemcpyDeviceToHost, c->stream);
+        if (prim_index) cudaMemcpyAsync(prim_index, c->d_pindex, npix * 4, cudaMemcpyDeviceToHost, c->stream);
+        if (prim_t) cudaMemcpyAsync(prim_t, c->d_pt, npix * 4, cudaMemcpyDeviceToHost, c->stream);
+        return cuda_err(c, cudaStreamSynchronize(c->stream), "probe");
+    }
     const DeviceScene S = make_device_scene(c, 0xffffffffu);
     launch_exact_frame(S, nullptr, c->d_radiance, c->d_ptype, c->d_pindex, c->d_pt, c->stream);
     if (radiance_out) cudaMemcpyAsync(radiance_out, c->d_radiance, npix * 12, cudaMemcpyDeviceToHost, c->stream);
@@ -170,6 +189,16 @@ int wgpt_counters(wgpt_ctx* c, wgpt_counter_block* out, int reset) {
     if (e != cudaSuccess) return cuda_err(c, e, "counters");
     out->rays = h[0]; out->node_visits = h[1]; out->tri_tests = h[2]; out->sphere_tests = h[3];
     out->quad_tests = h[4]; out->rng_draws = h[5]; out->samples = h[6]; out->stack_aborts = h[7];
+    return WGPT_OK;
+}
+
+int wgpt_fast_statistics(wgpt_ctx* c, wgpt_fast_stats* out) {
+    if (!c || !out) return WGPT_E_INVALID;
+    cudaSetDevice(c->cfg.device);
+    uint32_t v[8];
+    fast_stats(c, v);
+    out->wide_nodes = v[0]; out->wide_tris = v[1]; out->wide_levels = v[2]; out->pool_slots = v[3]; out->ring_frames = v[4];
+    out->fallback_rays = v[5]; out->iterations = v[6]; out->trace_fallback_rays = v[7];
     return WGPT_OK;
 }
 

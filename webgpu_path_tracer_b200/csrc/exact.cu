@@ -4,17 +4,10 @@
 // Restates /root/reference/shaders/main.wgsl:1-28, shootRay.wgsl:5-60, traceRay.wgsl:3-83.
 #include "kernels.cuh"
 #include "shade.cuh"
+#include "camera.cuh"
 #include "trace_binary.cuh"
 
 namespace wg {
-
-// shootRay.wgsl:54-60: normalize(viewMatrix * vec4(s, t, -fovFactor, 0)).xyz -- the vec4 is normalised
-__device__ __forceinline__ Ray camera_ray(const DeviceScene& S, v3 cam_origin, float s, float t) {
-    const v4 d = mul4(S.uniforms.viewMatrix, V3(s, t, -1.7320508075688774f), 0.0f);
-    const float l = fsq(fa(fa(fa(fm(d.x, d.x), fm(d.y, d.y)), fm(d.z, d.z)), fm(d.w, d.w)));
-    Ray r; r.o = cam_origin; r.d = V3(fd(d.x, l), fd(d.y, l), fd(d.z, l));
-    return r;
-}
 
 struct Primary { int type, index; float t; bool done; };
 
@@ -46,13 +39,8 @@ __device__ __forceinline__ v3 ray_color(const DeviceScene& S, Ray ray, uint32_t&
 
 // shootRay.wgsl:5-49 + main.wgsl:3-18
 __device__ __forceinline__ v3 compute_pixel(const DeviceScene& S, uint32_t pixelIndex, Counts* cnt, Primary& prim) {
-    const float W = S.uniforms.screenW, H = S.uniforms.screenH;
-    const float fi = (float)pixelIndex;
-    const float px = fs(fi, fm(W, truncf(fd(fi, W))));       // f32(idx) % W
-    const float py = fd(fi, W);                              // unfloored (quirk Q1)
-    const v3 cam_origin = mul4_xyz(S.uniforms.viewMatrix, V3s(0.0f), 1.0f);
-    uint32_t rng = pixelIndex + (uint32_t)S.uniforms.frameNum * 719393u;
-    if (cnt) cnt->rng += 0;
+    const PixelSetup ps = pixel_setup(S, pixelIndex);
+    uint32_t rng = pixel_seed(pixelIndex, S.uniforms.frameNum);
 
     ShadeState st;
     st.p = st.n = st.unit_w = st.u = st.v = V3s(0.0f);
@@ -61,31 +49,23 @@ __device__ __forceinline__ v3 compute_pixel(const DeviceScene& S, uint32_t pixel
     prim.done = false; prim.type = prim.index = -1; prim.t = 0.0f;
 
     v3 pix = V3s(0.0f);
-    const float aspect = fd(W, H);
     if (S.K.STRATIFY) {
-        const float sqrt_spp = (float)sqrt((double)S.K.NUM_SAMPLES);
-        const float recip = fd(1.0f, (float)((int)sqrt_spp));
+        const int side = strat_side(S);
         float numSamples = 0.0f;
-        for (float i = 0.0f; i < sqrt_spp; i += 1.0f) {
-            for (float j = 0.0f; j < sqrt_spp; j += 1.0f) {
-                const float rx = rand2D(rng);
-                const float sx = fm(aspect, fs(fm(2.0f, fd(fa(fs(px, 0.5f), fm(recip, fa(i, rx))), W)), 1.0f));
-                const float ry = rand2D(rng);
-                const float sy = fm(-1.0f, fs(fm(2.0f, fd(fa(fs(py, 0.5f), fm(recip, fa(j, ry))), H)), 1.0f));
+        for (int i = 0; i < side; i++) {
+            for (int j = 0; j < side; j++) {
+                const Ray r = sample_ray(S, ps, i, j, rng);
                 if (cnt) { cnt->rng += 2; cnt->samples++; }
-                pix = pix + ray_color(S, camera_ray(S, cam_origin, sx, sy), rng, cnt, st, prim);
+                pix = pix + ray_color(S, r, rng, cnt, st, prim);
                 numSamples += 1.0f;
             }
         }
         pix = pix / numSamples;
     } else {
         for (int i = 0; i < S.K.NUM_SAMPLES; i++) {
-            const float rx = rand2D(rng);
-            const float sx = fm(aspect, fs(fm(2.0f, fd(fa(fs(px, 0.5f), rx), W)), 1.0f));
-            const float ry = rand2D(rng);
-            const float sy = fm(-1.0f, fs(fm(2.0f, fd(fa(fs(py, 0.5f), ry), H)), 1.0f));
+            const Ray r = sample_ray(S, ps, 0, 0, rng);
             if (cnt) { cnt->rng += 2; cnt->samples++; }
-            pix = pix + ray_color(S, camera_ray(S, cam_origin, sx, sy), rng, cnt, st, prim);
+            pix = pix + ray_color(S, r, rng, cnt, st, prim);
         }
         pix = pix / (float)S.K.NUM_SAMPLES;
     }

@@ -1,0 +1,207 @@
+// fast.cu -- host orchestration of the fast path: builds the 8-wide BVH when bindings 5/9 change
+// (K2), owns the wavefront pool, and drives the stage kernels (K3/K4) in batches without
+// stalling on the device: the only host<->device traffic per batch is one 4-byte "finished" flag
+// read back asynchronously, one batch behind.
+#include <stdlib.h>
+#include <string.h>
+#include <algorithm>
+#include "context.h"
+#include "kernels.cuh"
+#include "wavefront.cuh"
+
+namespace wg {
+
+struct FastState {
+    // wide BVH
+    uint4* wide_nodes = nullptr; float4* wide_tris = nullptr; uint32_t* wide_scratch = nullptr;
+    uint32_t wide_cap = 0, wide_tri_cap = 0;
+    WideBuildStats wstats = {0, 0, 0, 0};
+    // wavefront
+    WfParams P;
+    void* pool_mem = nullptr;
+    uint32_t capacity = 0, ring = 0;
+    uint32_t* h_flag = nullptr;            // pinned: finished flag copies
+    cudaEvent_t flag_ev[2] = {nullptr, nullptr};
+    uint32_t* d_fallbacks = nullptr;
+    bool pool_ready = false;
+};
+
+static int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
+}
+
+static int ensure_wide(wgpt_ctx* c) {
+    if (!c->fast) c->fast = new FastState();
+    FastState* F = c->fast;
+    if (!c->wide_dirty) return WGPT_OK;
+    const int n_bvh = (int)(c->dbytes[9] / 48), n_tri = (int)(c->dbytes[5] / 96);
+    cudaError_t e;
+    if (n_bvh == 0) { F->wstats = {0, 0, 0, 0}; c->wide_dirty = false; return WGPT_OK; }
+    const uint32_t cap = (uint32_t)std::max(16, n_bvh / 2 + 16);
+    if (cap > F->wide_cap || (uint32_t)n_tri > F->wide_tri_cap) {
+        if (F->wide_nodes) cudaFree(F->wide_nodes);
+        if (F->wide_tris) cudaFree(F->wide_tris);
+        if (F->wide_scratch) cudaFree(F->wide_scratch);
+        F->wide_nodes = nullptr; F->wide_tris = nullptr; F->wide_scratch = nullptr;
+        if ((e = cudaMalloc((void**)&F->wide_nodes, (size_t)cap * 80)) != cudaSuccess ||
+            (e = cudaMalloc((void**)&F->wide_tris, (size_t)std::max(1, n_tri) * 48)) != cudaSuccess ||
+            (e = cudaMalloc((void**)&F->wide_scratch, wide_scratch_bytes(cap))) != cudaSuccess) return cuda_err(c, e, "wide bvh alloc");
+        F->wide_cap = cap; F->wide_tri_cap = (uint32_t)n_tri;
+    }
+    launch_wide_build((const BvhNode*)c->dbuf[9], n_bvh, (const Triangle*)c->dbuf[5], n_tri, F->wide_nodes, F->wide_tris,
+                      F->wide_cap, F->wide_scratch, c->stream);
+    c->last_launches += 1 + 2 * 48;
+    F->wstats = wide_build_stats(F->wide_scratch, c->stream);
+    if ((e = cudaGetLastError()) != cudaSuccess) return cuda_err(c, e, "wide bvh build");
+    if (F->wstats.overflow || F->wstats.n_tris != (uint32_t)n_tri)
+        return set_err(c, WGPT_E_INVALID, "binary BVH does not meet the flatten contract (pre-order, 1-triangle leaves, depth <= 48 wide levels)");
+    c->wide_dirty = false;
+    return WGPT_OK;
+}
+
+static WideBvh wide_view(FastState* F) {
+    WideBvh w; w.nodes = F->wide_nodes; w.tris = F->wide_tris; w.n_nodes = F->wstats.n_nodes; w.n_tris = F->wstats.n_tris;
+    return w;
+}
+
+static int ensure_pool(wgpt_ctx* c) {
+    FastState* F = c->fast;
+    if (F->pool_ready) return WGPT_OK;
+    const uint32_t npix = (uint32_t)c->cfg.width * c->cfg.height;
+    uint32_t cap = (uint32_t)env_int("WGPT_POOL", 0);
+    if (!cap) cap = std::min<uint64_t>(1u << 21, (uint64_t)c->shard_pixels * 4);
+    cap = std::max(1024u, (cap + 1023u) & ~1023u);
+    uint32_t ring = (uint32_t)env_int("WGPT_RING", 32);
+    ring = std::max(2u, std::min<uint32_t>(ring, WF_MAX_RING));
+    // one allocation, carved into 16-byte-aligned arrays
+    const size_t per_slot = 8 * 16 + (1 + WF_CLASSES) * 4;
+    const size_t bytes = (size_t)cap * per_slot + (size_t)ring * npix * 16 + 32 * 256;
+    cudaError_t e;
+    if ((e = cudaMalloc(&F->pool_mem, bytes)) != cudaSuccess) return cuda_err(c, e, "wavefront pool alloc");
+    if ((e = cudaMemsetAsync(F->pool_mem, 0, bytes, c->stream)) != cudaSuccess) return cuda_err(c, e, "wavefront pool clear");
+    char* p = (char*)F->pool_mem;
+    auto carve = [&](size_t n) { char* r = p; p += (n + 255) & ~(size_t)255; return r; };
+    WfParams& P = F->P;
+    memset(&P, 0, sizeof(P));
+    P.ctl = (WfControl*)carve(sizeof(WfControl));
+    P.pool.ro = (float4*)carve((size_t)cap * 16);  P.pool.rd = (float4*)carve((size_t)cap * 16);
+    P.pool.thr = (float4*)carve((size_t)cap * 16); P.pool.acc = (float4*)carve((size_t)cap * 16);
+    P.pool.pix = (float4*)carve((size_t)cap * 16); P.pool.hit = (float4*)carve((size_t)cap * 16);
+    P.pool.hid = (int4*)carve((size_t)cap * 16);   P.pool.misc = (uint4*)carve((size_t)cap * 16);
+    P.pool.capacity = cap;
+    P.q_extend = (uint32_t*)carve((size_t)cap * 4);
+    for (int k = 0; k < WF_CLASSES; k++) P.q_shade[k] = (uint32_t*)carve((size_t)cap * 4);
+    P.stage = (float4*)carve((size_t)ring * npix * 16);
+    P.ring = ring;
+    P.items_per_frame = c->shard_pixels;
+    if ((size_t)(p - (char*)F->pool_mem) > bytes) return set_err(c, WGPT_E_NOMEM, "pool carve overflow");
+    F->capacity = cap; F->ring = ring;
+    if ((e = cudaMallocHost((void**)&F->h_flag, 64)) != cudaSuccess) return cuda_err(c, e, "pinned flag");
+    memset(F->h_flag, 0, 64);
+    cudaEventCreateWithFlags(&F->flag_ev[0], cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&F->flag_ev[1], cudaEventDisableTiming);
+    if ((e = cudaMalloc((void**)&F->d_fallbacks, 4)) != cudaSuccess) return cuda_err(c, e, "fallback counter");
+    cudaMemsetAsync(F->d_fallbacks, 0, 4, c->stream);
+    F->pool_ready = true;
+    return WGPT_OK;
+}
+
+static int check_materials(wgpt_ctx* c) {
+    const Material* m = (const Material*)c->hbuf[8].data();
+    for (size_t i = 0; i < c->hbuf[8].size() / 64; i++) {
+        const float t = m[i].material_type;
+        if (!(t == 0.0f || t == 1.0f || t == 2.0f || t == 3.0f))
+            return set_err(c, WGPT_E_INVALID, "fast mode shades material_type 0..3 only (header.wgsl:4-8); use exact mode for others");
+    }
+    return WGPT_OK;
+}
+
+int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_first, int* d_ptype, int* d_pindex, float* d_pt) {
+    int rc = check_materials(c);
+    if (rc) return rc;
+    if ((rc = ensure_wide(c)) != WGPT_OK) return rc;
+    if ((rc = ensure_pool(c)) != WGPT_OK) return rc;
+    FastState* F = c->fast;
+    // frames of this strata shard: f in [first, first+n) with f % world == rank
+    const int world = c->cfg.strata_world, rank = c->cfg.strata_rank;
+    int f0 = first_frame;
+    while (world > 1 && (f0 % world) != rank) f0++;
+    const int last = first_frame + n_frames;
+    const uint32_t my_frames = f0 < last ? (uint32_t)((last - 1 - f0) / world + 1) : 0u;
+    if (my_frames == 0) return WGPT_OK;
+    WfParams P = F->P;
+    P.frame0 = f0; P.frame_stride = world;
+    P.prim_type = d_ptype; P.prim_index = d_pindex; P.prim_t = d_pt;
+    const DeviceScene S = make_device_scene(c, 0xffffffffu);
+    const WideBvh WB = wide_view(F);
+    wf_launch_init(P, my_frames, c->stream);
+    c->last_launches += 1;
+    const int batch = std::max(1, env_int("WGPT_BATCH", 8));
+    F->h_flag[0] = F->h_flag[1] = 0;
+    for (int b = 0;; b++) {
+        for (int i = 0; i < batch; i++) wf_launch_iteration(S, WB, P, (float4*)c->dbuf[3], reset_first, c->stream);
+        c->last_launches += (uint64_t)batch * WF_LAUNCHES_PER_ITERATION;
+        cudaMemcpyAsync(&F->h_flag[b & 1], &P.ctl->finished, 4, cudaMemcpyDeviceToHost, c->stream);
+        cudaEventRecord(F->flag_ev[b & 1], c->stream);
+        if (b >= 1) {                          // look at the previous batch's flag: the device stays one batch ahead
+            cudaError_t e = cudaEventSynchronize(F->flag_ev[(b - 1) & 1]);
+            if (e != cudaSuccess) return cuda_err(c, e, "wavefront batch");
+            if (F->h_flag[(b - 1) & 1]) break;
+        }
+        if (b > 4000000) return set_err(c, WGPT_E_STATE, "wavefront did not converge");
+    }
+    return cuda_err(c, cudaGetLastError(), "fast_render");
+}
+
+int fast_render(wgpt_ctx* c, int first_frame, int n_frames, int reset_first) {
+    return fast_render_probe(c, first_frame, n_frames, reset_first, nullptr, nullptr, nullptr);
+}
+
+int fast_trace_rays(wgpt_ctx* c, int n, const float* d_rays, const uint32_t* d_seeds, int* d_type, int* d_index, float* d_t) {
+    int rc = ensure_wide(c);
+    if (rc) return rc;
+    FastState* F = c->fast;
+    if (!F->d_fallbacks) {
+        cudaError_t e = cudaMalloc((void**)&F->d_fallbacks, 4);
+        if (e != cudaSuccess) return cuda_err(c, e, "fallback counter");
+        cudaMemsetAsync(F->d_fallbacks, 0, 4, c->stream);
+    }
+    if (!c->have_uniforms) memset(&c->uniforms, 0, sizeof(c->uniforms));
+    const DeviceScene S = make_device_scene(c, 0xffffffffu);
+    launch_trace_rays_wide(S, wide_view(F), n, d_rays, d_seeds, d_type, d_index, d_t, F->d_fallbacks, c->stream);
+    return cuda_err(c, cudaGetLastError(), "fast_trace_rays");
+}
+
+// fallbacks (rays re-traced in reference order) of the last render + of trace_rays since creation; wide BVH stats
+int fast_stats(wgpt_ctx* c, uint32_t out[8]) {
+    memset(out, 0, 32);
+    FastState* F = c->fast;
+    if (!F) return WGPT_OK;
+    out[0] = F->wstats.n_nodes; out[1] = F->wstats.n_tris; out[2] = F->wstats.n_levels; out[3] = F->capacity; out[4] = F->ring;
+    cudaStreamSynchronize(c->stream);
+    if (F->pool_ready) {
+        WfControl h;
+        cudaMemcpy(&h, F->P.ctl, sizeof(h), cudaMemcpyDeviceToHost);
+        out[5] = h.fallbacks; out[6] = h.iterations;
+    }
+    if (F->d_fallbacks) cudaMemcpy(&out[7], F->d_fallbacks, 4, cudaMemcpyDeviceToHost);
+    return WGPT_OK;
+}
+
+void fast_destroy(wgpt_ctx* c) {
+    FastState* F = c->fast;
+    if (!F) return;
+    if (F->wide_nodes) cudaFree(F->wide_nodes);
+    if (F->wide_tris) cudaFree(F->wide_tris);
+    if (F->wide_scratch) cudaFree(F->wide_scratch);
+    if (F->pool_mem) cudaFree(F->pool_mem);
+    if (F->h_flag) cudaFreeHost(F->h_flag);
+    if (F->flag_ev[0]) cudaEventDestroy(F->flag_ev[0]);
+    if (F->flag_ev[1]) cudaEventDestroy(F->flag_ev[1]);
+    if (F->d_fallbacks) cudaFree(F->d_fallbacks);
+    delete F;
+    c->fast = nullptr;
+}
+
+}  // namespace wg

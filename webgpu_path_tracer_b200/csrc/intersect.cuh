@@ -131,10 +131,10 @@ __device__ __forceinline__ bool tri_test(v3 A, v3 B, v3 C, const Ray& oray, floa
 // common.wgsl:245-256
 __device__ __forceinline__ bool hit_aabb(v3 mn, v3 mx, float tmin, float tmax, v3 o, v3 invDir) {
     const v3 t0 = (mn - o) * invDir, t1 = (mx - o) * invDir;
-    const float sx = pmin(t0.x, t1.x), sy = pmin(t0.y, t1.y), sz = pmin(t0.z, t1.z);
-    const float bx = pmax(t0.x, t1.x), by = pmax(t0.y, t1.y), bz = pmax(t0.z, t1.z);
-    const float t_min = pmax(tmin, pmax(sx, pmax(sy, sz)));
-    const float t_max = pmin(tmax, pmin(bx, pmin(by, bz)));
+    const float sx = bmin(t0.x, t1.x), sy = bmin(t0.y, t1.y), sz = bmin(t0.z, t1.z);
+    const float bx = bmax(t0.x, t1.x), by = bmax(t0.y, t1.y), bz = bmax(t0.z, t1.z);
+    const float t_min = bmax(tmin, bmax(sx, bmax(sy, sz)));
+    const float t_max = bmin(tmax, bmin(bx, bmin(by, bz)));
     return t_max > t_min;
 }
 

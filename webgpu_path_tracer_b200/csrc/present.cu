@@ -49,6 +49,13 @@ __global__ void __launch_bounds__(256) k_accumulate(float4* __restrict__ fb, con
     }
 }
 
+__global__ void __launch_bounds__(256) k_fb_to_rgb(const float4* __restrict__ fb, float* __restrict__ rgb, uint32_t npix) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        const float4 s = fb[i];
+        rgb[3 * i] = s.x; rgb[3 * i + 1] = s.y; rgb[3 * i + 2] = s.z;
+    }
+}
+
 static unsigned stream_grid(uint32_t n, unsigned threads) {
     unsigned blocks = (n + threads - 1) / threads;
     const unsigned cap = 148u * 8u;          // 148 SMs x 8 resident 256-thread CTAs
@@ -58,6 +65,10 @@ static unsigned stream_grid(uint32_t n, unsigned threads) {
 void launch_present(const float4* fb_in, float4* fb_clear, float4* rgba_out, uchar4* rgba8_out, uint32_t npix,
                     float frameNum, int clear, cudaStream_t stream) {
     k_present<<<stream_grid(npix, 256), 256, 0, stream>>>(fb_in, fb_clear, rgba_out, rgba8_out, npix, frameNum, clear);
+}
+
+void launch_fb_to_rgb(const float4* fb, float* rgb, uint32_t npix, cudaStream_t stream) {
+    k_fb_to_rgb<<<stream_grid(npix, 256), 256, 0, stream>>>(fb, rgb, npix);
 }
 
 void launch_accumulate(float4* fb, const float4* frame, uint32_t npix, int reset, cudaStream_t stream) {

@@ -1,0 +1,69 @@
+// wavefront.cuh -- state of the persistent-thread wavefront integrator (K3): SoA path pool, ray /
+// shade queues, the device-resident control block, and the frame staging ring that keeps the
+// per-pixel float sum in FRAME ORDER (main.wgsl:24-27 adds one frame at a time) while many frames
+// are in flight.
+#pragma once
+#include <stdint.h>
+#include <cuda_runtime.h>
+#include "scene.cuh"
+#include "wide_bvh.cuh"
+
+namespace wg {
+
+#define WF_MAX_RING 64
+#define WF_CLASSES 6            // 0..3 material_type of the hit, 4 miss, 5 idle (slot waiting for work)
+#define WF_KIND_IDLE (-2)
+
+// One path per slot, structure-of-arrays, 16-byte elements (LDG.128 / STG.128).
+struct PathPool {
+    float4* ro;      // ray origin.xyz
+    float4* rd;      // ray direction.xyz
+    float4* thr;     // throughput.xyz
+    float4* acc;     // accumulated radiance of the current sample .xyz
+    float4* pix;     // pixColor of the (pixel, frame) so far .xyz, .w = samples taken (stratified divisor)
+    float4* hit;     // t, uu, vv of the last closest-hit query
+    int4*   hid;     // kind (HitKind / WF_KIND_IDLE), index, mat_id, -
+    uint4*  misc;    // rng state, shard-local pixel i, frame ordinal k, (bounce << 16) | sample counter
+    uint32_t capacity;
+};
+
+struct WfControl {
+    unsigned long long next_work;      // next (frame ordinal, pixel) item to hand out
+    unsigned long long work_limit;     // items below this may start (ring window)
+    unsigned long long total_work;
+    uint32_t n_extend;                 // rays queued for the extend stage
+    uint32_t extend_cursor;            // persistent-warp fetch cursor
+    uint32_t n_shade[WF_CLASSES];
+    uint32_t shade_off[WF_CLASSES + 1];
+    uint32_t shade_cursor;
+    uint32_t done[WF_MAX_RING];        // finished items per ring slot
+    uint32_t acc_k;                    // next frame ordinal to fold into binding 3
+    uint32_t ready_first, n_ready;     // frames the accumulate pass folds this iteration
+    uint32_t n_frames;                 // frame ordinals to render in this call
+    uint32_t finished;
+    uint32_t fallbacks;                // rays re-traced with the reference-order walk
+    uint32_t iterations;
+};
+
+struct WfParams {
+    PathPool pool;
+    WfControl* ctl;
+    uint32_t* q_extend;                // slot ids, capacity entries
+    uint32_t* q_shade[WF_CLASSES];     // slot ids per class, capacity entries each
+    float4* stage;                     // ring x W*H: (pixColor, 1)
+    uint32_t ring;                     // frames in flight
+    uint32_t items_per_frame;          // shard.n_pixels
+    int frame0, frame_stride;          // frame number of ordinal k = frame0 + k * frame_stride
+    // optional probe outputs (first closest-hit query of every pixel), indexed by pixel
+    int* prim_type; int* prim_index; float* prim_t;
+};
+
+// wavefront.cu
+void wf_launch_init(const WfParams& P, uint32_t n_frames, cudaStream_t stream);
+void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
+                         cudaStream_t stream);
+#define WF_LAUNCHES_PER_ITERATION 5
+void launch_trace_rays_wide(const DeviceScene& S, const WideBvh& WB, int n, const float* rays, const uint32_t* seeds,
+                            int* out_type, int* out_index, float* out_t, uint32_t* fallbacks, cudaStream_t stream);
+
+}  // namespace wg
