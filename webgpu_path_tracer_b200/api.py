@@ -19,7 +19,7 @@ COUNTER_NAMES = ("rays", "node_visits", "tri_tests", "sphere_tests", "quad_tests
 EXPORTS = ("wgpt_default_config", "wgpt_create", "wgpt_destroy", "wgpt_last_error", "wgpt_write_buffer",
            "wgpt_read_buffer", "wgpt_device_ptr", "wgpt_dispatch", "wgpt_render", "wgpt_present", "wgpt_probe",
            "wgpt_trace_rays", "wgpt_counters", "wgpt_set_counters", "wgpt_last_timing", "wgpt_synchronize",
-           "wgpt_pinned_math", "wgpt_fast_statistics")
+           "wgpt_pinned_math", "wgpt_fast_statistics", "wgpt_set_stage_profiling", "wgpt_stage_timings")
 
 
 class WgptError(RuntimeError):
@@ -78,6 +78,8 @@ def load_library(path=None):
     L.wgpt_synchronize.argtypes = [vp]
     L.wgpt_pinned_math.argtypes = [vp, i32, i32, vp, vp, vp]
     L.wgpt_fast_statistics.argtypes = [vp, C.POINTER(FastStats)]
+    L.wgpt_set_stage_profiling.argtypes = [vp, i32]
+    L.wgpt_stage_timings.argtypes = [vp, C.POINTER(C.c_float * 4), C.POINTER(C.c_uint64 * 4)]
     if path is None:
         _lib = L
     return L
@@ -201,6 +203,15 @@ class PathTracer:
         st = FastStats()
         self._ck(self.L.wgpt_fast_statistics(self.h, C.byref(st)), "wgpt_fast_statistics")
         return {n: int(getattr(st, n)) for n, _ in FastStats._fields_}
+
+    def set_stage_profiling(self, enabled):
+        self._ck(self.L.wgpt_set_stage_profiling(self.h, int(enabled)), "wgpt_set_stage_profiling")
+
+    def stage_timings(self):
+        ms, n = (C.c_float * 4)(), (C.c_uint64 * 4)()
+        self._ck(self.L.wgpt_stage_timings(self.h, C.byref(ms), C.byref(n)), "wgpt_stage_timings")
+        names = ("extend", "shade", "control_accumulate", "wide_build")
+        return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(names)}
 
     def pinned_math(self, fn, x, y=None):
         names = {"sin": 0, "cos": 1, "acos": 2, "log": 3, "pow": 4}

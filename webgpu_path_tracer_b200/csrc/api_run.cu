@@ -202,6 +202,18 @@ int wgpt_fast_statistics(wgpt_ctx* c, wgpt_fast_stats* out) {
     return WGPT_OK;
 }
 
+int wgpt_set_stage_profiling(wgpt_ctx* c, int enabled) {
+    if (!c) return WGPT_E_INVALID;
+    c->stage_profiling = enabled != 0;
+    return WGPT_OK;
+}
+
+int wgpt_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]) {
+    if (!c || !ms || !launches) return WGPT_E_INVALID;
+    cudaSetDevice(c->cfg.device);
+    return fast_stage_timings(c, ms, launches);
+}
+
 int wgpt_synchronize(wgpt_ctx* c) {
     if (!c) return WGPT_E_INVALID;
     cudaSetDevice(c->cfg.device);

@@ -29,6 +29,7 @@ struct wgpt_ctx {
     float* d_radiance = nullptr; int* d_ptype = nullptr; int* d_pindex = nullptr; float* d_pt = nullptr;
     wg::FastState* fast = nullptr;         // wide BVH + wavefront pool (fast.cu)
     bool wide_dirty = true;
+    bool stage_profiling = false;
     // summary of the big device-only tables, gathered at upload time for validation
     int tri_mesh_max = -1; bool tri_bad = false;
     long long bvh_prim_end_max = 0; bool bvh_bad = false;
@@ -47,6 +48,7 @@ int validate_scene(wgpt_ctx* c);
 int fast_render(wgpt_ctx* c, int first_frame, int n_frames, int reset_first);
 int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_first, int* d_ptype, int* d_pindex, float* d_pt);
 int fast_stats(wgpt_ctx* c, uint32_t out[8]);
+int fast_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]);
 int fast_trace_rays(wgpt_ctx* c, int n, const float* d_rays, const uint32_t* d_seeds, int* d_type, int* d_index, float* d_t);
 void fast_destroy(wgpt_ctx* c);
 }

@@ -5,6 +5,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
+#include <vector>
 #include "context.h"
 #include "kernels.cuh"
 #include "wavefront.cuh"
@@ -24,7 +25,39 @@ struct FastState {
     cudaEvent_t flag_ev[2] = {nullptr, nullptr};
     uint32_t* d_fallbacks = nullptr;
     bool pool_ready = false;
+    // stage profiling: a ring of event quadruples, folded into the sums whenever it fills up
+    std::vector<cudaEvent_t> prof_ev;
+    size_t prof_used = 0;
+    double prof_ms[4] = {0, 0, 0, 0};
+    uint64_t prof_launches[4] = {0, 0, 0, 0};
+    cudaEvent_t wide_ev[2] = {nullptr, nullptr};
+    bool wide_timed = false;
 };
+
+static const size_t PROF_QUADS = 2048;
+
+static void prof_fold(FastState* F) {
+    if (!F->prof_used) return;
+    cudaEventSynchronize(F->prof_ev[4 * (F->prof_used - 1) + 3]);
+    for (size_t i = 0; i < F->prof_used; i++) {
+        float a = 0, b = 0, c2 = 0;
+        cudaEventElapsedTime(&a, F->prof_ev[4 * i], F->prof_ev[4 * i + 1]);
+        cudaEventElapsedTime(&b, F->prof_ev[4 * i + 1], F->prof_ev[4 * i + 2]);
+        cudaEventElapsedTime(&c2, F->prof_ev[4 * i + 2], F->prof_ev[4 * i + 3]);
+        F->prof_ms[0] += a; F->prof_ms[1] += b; F->prof_ms[2] += c2;
+        F->prof_launches[0] += 1; F->prof_launches[1] += 2; F->prof_launches[2] += 2;
+    }
+    F->prof_used = 0;
+}
+
+static cudaEvent_t* prof_next(FastState* F) {
+    if (F->prof_ev.empty()) {
+        F->prof_ev.resize(4 * PROF_QUADS);
+        for (auto& e : F->prof_ev) cudaEventCreate(&e);
+    }
+    if (F->prof_used == PROF_QUADS) prof_fold(F);
+    return &F->prof_ev[4 * F->prof_used++];
+}
 
 static int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
@@ -49,9 +82,14 @@ static int ensure_wide(wgpt_ctx* c) {
             (e = cudaMalloc((void**)&F->wide_scratch, wide_scratch_bytes(cap))) != cudaSuccess) return cuda_err(c, e, "wide bvh alloc");
         F->wide_cap = cap; F->wide_tri_cap = (uint32_t)n_tri;
     }
+    if (c->stage_profiling) {
+        if (!F->wide_ev[0]) { cudaEventCreate(&F->wide_ev[0]); cudaEventCreate(&F->wide_ev[1]); }
+        cudaEventRecord(F->wide_ev[0], c->stream);
+    }
     launch_wide_build((const BvhNode*)c->dbuf[9], n_bvh, (const Triangle*)c->dbuf[5], n_tri, F->wide_nodes, F->wide_tris,
                       F->wide_cap, F->wide_scratch, c->stream);
     c->last_launches += 1 + 2 * 48;
+    if (c->stage_profiling) { cudaEventRecord(F->wide_ev[1], c->stream); F->wide_timed = true; }
     F->wstats = wide_build_stats(F->wide_scratch, c->stream);
     if ((e = cudaGetLastError()) != cudaSuccess) return cuda_err(c, e, "wide bvh build");
     if (F->wstats.overflow || F->wstats.n_tris != (uint32_t)n_tri)
@@ -140,7 +178,8 @@ int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_firs
     const int batch = std::max(1, env_int("WGPT_BATCH", 8));
     F->h_flag[0] = F->h_flag[1] = 0;
     for (int b = 0;; b++) {
-        for (int i = 0; i < batch; i++) wf_launch_iteration(S, WB, P, (float4*)c->dbuf[3], reset_first, c->stream);
+        for (int i = 0; i < batch; i++)
+            wf_launch_iteration(S, WB, P, (float4*)c->dbuf[3], reset_first, c->stream, c->stage_profiling ? prof_next(F) : nullptr);
         c->last_launches += (uint64_t)batch * WF_LAUNCHES_PER_ITERATION;
         cudaMemcpyAsync(&F->h_flag[b & 1], &P.ctl->finished, 4, cudaMemcpyDeviceToHost, c->stream);
         cudaEventRecord(F->flag_ev[b & 1], c->stream);
@@ -189,9 +228,26 @@ int fast_stats(wgpt_ctx* c, uint32_t out[8]) {
     return WGPT_OK;
 }
 
+int fast_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]) {
+    for (int i = 0; i < 4; i++) { ms[i] = 0.0f; launches[i] = 0; }
+    FastState* F = c->fast;
+    if (!F) return WGPT_OK;
+    prof_fold(F);
+    if (F->wide_timed) {
+        float t = 0;
+        cudaEventSynchronize(F->wide_ev[1]);
+        cudaEventElapsedTime(&t, F->wide_ev[0], F->wide_ev[1]);
+        F->prof_ms[3] += t; F->prof_launches[3] += 1 + 2 * 48; F->wide_timed = false;
+    }
+    for (int i = 0; i < 4; i++) { ms[i] = (float)F->prof_ms[i]; launches[i] = F->prof_launches[i]; F->prof_ms[i] = 0; F->prof_launches[i] = 0; }
+    return WGPT_OK;
+}
+
 void fast_destroy(wgpt_ctx* c) {
     FastState* F = c->fast;
     if (!F) return;
+    for (auto& e : F->prof_ev) cudaEventDestroy(e);
+    if (F->wide_ev[0]) { cudaEventDestroy(F->wide_ev[0]); cudaEventDestroy(F->wide_ev[1]); }
     if (F->wide_nodes) cudaFree(F->wide_nodes);
     if (F->wide_tris) cudaFree(F->wide_tris);
     if (F->wide_scratch) cudaFree(F->wide_scratch);

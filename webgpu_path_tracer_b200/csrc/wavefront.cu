@@ -332,19 +332,23 @@ void wf_launch_init(const WfParams& P, uint32_t n_frames, cudaStream_t stream) {
 }
 
 void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, cudaEvent_t* ev) {
     const unsigned extend_blocks = 148u * 8u;                // persistent: 8 CTAs of 4 warps per SM
+    if (ev) cudaEventRecord(ev[0], stream);
     if (S.counters) k_wf_extend<true><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
+    if (ev) cudaEventRecord(ev[1], stream);
     k_wf_ctl_mid<<<1, 32, 0, stream>>>(P);
     const unsigned shade_blocks = (P.pool.capacity + 255u) / 256u;
     if (S.counters) k_wf_shade<true><<<shade_blocks, 256, 0, stream>>>(S, P);
     else k_wf_shade<false><<<shade_blocks, 256, 0, stream>>>(S, P);
+    if (ev) cudaEventRecord(ev[2], stream);
     k_wf_ctl_end<<<1, 32, 0, stream>>>(P);
     const uint32_t npix = (uint32_t)S.W * (uint32_t)S.H;
     unsigned acc_blocks = (npix + 255u) / 256u;
     if (acc_blocks > 148u * 8u) acc_blocks = 148u * 8u;
     k_wf_accumulate<<<acc_blocks, 256, 0, stream>>>(P, fb, npix, reset_first);
+    if (ev) cudaEventRecord(ev[3], stream);
 }
 
 // closest-hit hook over the wide BVH (wgpt_trace_rays in fast mode)

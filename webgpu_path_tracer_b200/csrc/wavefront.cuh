@@ -60,8 +60,9 @@ struct WfParams {
 
 // wavefront.cu
 void wf_launch_init(const WfParams& P, uint32_t n_frames, cudaStream_t stream);
+// ev: optional 4 events recorded before extend, after extend, after shade, after accumulate
 void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
-                         cudaStream_t stream);
+                         cudaStream_t stream, cudaEvent_t* ev = nullptr);
 #define WF_LAUNCHES_PER_ITERATION 5
 void launch_trace_rays_wide(const DeviceScene& S, const WideBvh& WB, int n, const float* rays, const uint32_t* seeds,
                             int* out_type, int* out_index, float* out_t, uint32_t* fallbacks, cudaStream_t stream);
