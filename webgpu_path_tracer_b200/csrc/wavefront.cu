@@ -1,18 +1,20 @@
 // wavefront.cu -- K3: the persistent-thread wavefront integrator.
 //
-// Stages per iteration (one bounce of every live path), all sized from the device-resident
-// control block, no host round trip:
-//   extend   persistent warps pull batches of 32 ray slots from the extend queue, run the
-//            closest-hit query (spheres/quads + 8-wide BVH, trace_wide.cuh) and append the slot to
-//            the shade queue of its material class with one warp-aggregated atomic per class
-//            (ballot + popc compaction) => material-sorted shading;
-//   shade    one thread per queued slot, classes laid out back to back so warps are homogeneous:
+// Path state lives in a structure-of-arrays pool (one slot per path); one iteration advances every
+// live path by one bounce with two kernels sized from a device-resident control block (no host
+// round trip):
+//   extend   persistent warps.  Every lane owns one ray; lanes that finish pull the next slot id
+//            from the compacted ray queue with one warp-aggregated atomic (ballot + popc), so a
+//            warp never idles behind its longest traversal (dynamic ray fetch).  Closest hit =
+//            spheres/quads + 8-wide BVH (trace_wide.cuh); result and shade class go back to the slot.
+//   shade    threads map to slots in slot order (coalesced SoA); each block first sorts its 256
+//            slots by material class in shared memory so warps shade one material at a time;
 //            miss -> background; hit -> emission, BSDF sample, mixture pdf against the light quad
 //            (the reference's "shadow" term is the analytic light_pdf, importanceSampling.wgsl:88-125:
-//            it casts no occlusion ray), Russian roulette; finished samples are folded into the
-//            pixel, finished (pixel, frame) items are written to the staging ring, and the slot
-//            REGENERATES from the next work item (generate stage) before being compacted
-//            (block-level ballot/prefix) into the next extend queue;
+//            it casts no occlusion ray), Russian roulette.  Finished samples fold into the pixel,
+//            finished (pixel, frame) items go to the staging ring, and the slot REGENERATES from
+//            the next work item (generate stage).  Live rays are compacted (block-level
+//            ballot/prefix, one atomic per block) into the next ray queue.
 //   accumulate  K4: frames whose every item finished are added to binding 3 in frame order.
 // The RNG stream of a (pixel, frame) item lives in its slot, so the draw order equals the
 // reference's whatever the schedule; all arithmetic is pinned.
@@ -23,23 +25,22 @@
 
 namespace wg {
 
+#ifndef WF_REFILL_BELOW
+#define WF_REFILL_BELOW 22      // refill the warp when fewer lanes than this still traverse
+#endif
+
 __device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
 
 __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < P.pool.capacity) {
-        P.q_extend[i] = i;
-        P.pool.hid[i] = make_int4(WF_KIND_IDLE, -1, -1, 0);
-    }
+    if (i < P.pool.capacity) P.pool.hid[i] = make_int4(HIT_NONE, -1, -1, WF_CLS_IDLE);
     if (i == 0) {
         WfControl* c = P.ctl;
         c->next_work = 0;
         c->total_work = (unsigned long long)n_frames * P.items_per_frame;
         const unsigned long long win = (unsigned long long)P.ring * P.items_per_frame;
         c->work_limit = win < c->total_work ? win : c->total_work;
-        c->n_extend = P.pool.capacity; c->extend_cursor = 0;
-        for (int k = 0; k < WF_CLASSES; k++) { c->n_shade[k] = 0; c->shade_off[k] = 0; }
-        c->shade_off[WF_CLASSES] = 0; c->shade_cursor = 0;
+        c->n_extend = 0; c->extend_cursor = 0; c->n_next = 0;
         for (int k = 0; k < WF_MAX_RING; k++) c->done[k] = 0;
         c->acc_k = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
         c->finished = n_frames == 0 ? 1u : 0u; c->fallbacks = 0; c->iterations = 0;
@@ -54,51 +55,121 @@ __global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, Wf
     const uint32_t lane = threadIdx.x & 31u;
     Counts c = {0, 0, 0, 0, 0, 0, 0, 0};
     unsigned fallbacks = 0;
+
+    // per-lane ray + traversal state
+    bool has = false, exhausted = (n == 0);
+    uint32_t slot = 0, rng = 0, rng_in = 0, miscw = 0, miscy = 0;
+    Ray ray; ray.o = ray.d = V3s(0.0f);
+    WideRay wr; wr.idx = wr.idy = wr.idz = 0.0f; wr.octinv = 0;
+    ObjRayCache oc; oc.reset();
+    HitLite h, h0;
+    h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1; h0 = h;
+    float closest = WGPT_MAX_FLOAT, c0 = WGPT_MAX_FLOAT;
+    bool hit_a = false, hit_t = false, ambiguous = false;
+    uint2 G = make_uint2(0u, 0u);
+    uint2 stack[WIDE_STACK];
+    int sp = 0;
+
     while (true) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(&ctl->extend_cursor, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        const uint32_t idx = base + lane;
-        int cls = -1;
-        uint32_t slot = 0;
-        if (idx < n) {
-            slot = P.q_extend[idx];
-            const int4 hid_in = P.pool.hid[slot];
-            if (hid_in.x == WF_KIND_IDLE) {
-                cls = 5;
-            } else {
-                const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot];
-                Ray ray; ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
-                const uint4 misc = P.pool.misc[slot];
-                uint32_t rng = misc.x;
-                ObjRayCache oc;
-                HitLite h; h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1;
-                const bool hit = hitScene_wide(S, WB, ray, rng, COUNT ? &c : nullptr, oc, h, &fallbacks);
-                if (rng != misc.x) P.pool.misc[slot].x = rng;
+        // ---- dynamic ray fetch: every lane without a ray takes the next queue entry ----
+        if (!exhausted) {
+            const uint32_t m = __ballot_sync(0xffffffffu, !has);
+            if (m) {
+                const int leader = __ffs((int)m) - 1;
+                const uint32_t want = (uint32_t)__popc(m);
+                uint32_t base = 0;
+                if ((int)lane == leader) base = atomicAdd(&ctl->extend_cursor, want);
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (!has) {
+                    const uint32_t idx = base + (uint32_t)__popc(m & lanemask_lt());
+                    if (idx < n) {
+                        slot = P.q_extend[idx];
+                        const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot];
+                        const uint4 misc = P.pool.misc[slot];
+                        ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
+                        rng = rng_in = misc.x; miscy = misc.y; miscw = misc.w;
+                        // spheres + quads (hitRay.wgsl:6-40), then set the BVH walk up
+                        closest = WGPT_MAX_FLOAT;
+                        h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1;
+                        if (COUNT) c.rays++;
+                        oc.reset();
+                        hit_a = hit_analytic(S, ray, rng, COUNT ? &c : nullptr, closest, h);
+                        h0 = h; c0 = closest;
+                        hit_t = false; ambiguous = false; sp = 0;
+                        wr = make_wide_ray(ray);
+                        G = WB.n_nodes ? make_uint2(0u, 0x80000000u) : make_uint2(0u, 0u);
+                        has = true;
+                    }
+                }
+                if (base + want >= n) exhausted = true;
+            }
+        }
+        if (__ballot_sync(0xffffffffu, has) == 0) break;        // queue drained and every lane finished
+
+        // ---- traverse: one wide-node visit per step for every lane that still has one pending ----
+        while (true) {
+            if (has && (G.y & 0xff000000u)) {
+                const uint32_t bit = 31u - (uint32_t)__clz((int)(G.y & 0xff000000u));
+                const uint32_t hits_imask = G.y;
+                bool abort_walk = false;
+                G.y &= ~(1u << bit);
+                if (G.y & 0xff000000u) {
+                    if (sp >= WIDE_STACK) abort_walk = true;        // deeper than the wide stack: reference walk decides
+                    else stack[sp++] = G;
+                }
+                if (!abort_walk) {
+                    const uint32_t sl = (bit - 24u) ^ wr.octinv;
+                    const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << sl) & 0xffu);
+                    uint32_t child_base, tri_base, imask;
+                    if (COUNT) c.nodes++;
+                    const uint32_t hm = wide_node_hits(WB.nodes, G.x + rel, ray, wr, closest, child_base, tri_base, imask);
+                    G = make_uint2(child_base, (hm & 0xff000000u) | imask);
+                    uint32_t tm = hm & 0x00ffffffu;
+                    while (tm) {
+                        const int b = __ffs((int)tm) - 1;
+                        tm &= tm - 1u;
+                        const float4* t = &WB.tris[3 * (size_t)(tri_base + (uint32_t)b)];
+                        const float4 A = __ldg(&t[0]), B = __ldg(&t[1]), C = __ldg(&t[2]);
+                        oc.fetch(S, __float_as_int(B.w), ray);
+                        float dst, uu, vv;
+                        if (COUNT) c.tris++;
+                        if (tri_test(V3(A.x, A.y, A.z), V3(B.x, B.y, B.z), V3(C.x, C.y, C.z), oc.oray, WGPT_RAY_TMIN, closest, dst, uu, vv)) {
+                            if (hit_t && dst == closest) abort_walk = true;      // equal-distance triangles: visit order decides
+                            hit_t = true; closest = dst;
+                            h.t = dst; h.kind = HIT_TRI; h.index = __float_as_int(A.w); h.uu = uu; h.vv = vv;
+                            h.mat_id = oc.m.material_id;
+                        }
+                    }
+                }
+                if (abort_walk) { ambiguous = true; G.y = 0u; sp = 0; }
+                else if (!(G.y & 0xff000000u) && sp > 0) G = stack[--sp];
+            }
+            // lanes whose walk is over write their result back and free the lane
+            if (has && !(G.y & 0xff000000u)) {
+                if (ambiguous) {                                   // re-derive in reference order
+                    h = h0; closest = c0;
+                    hit_t = hit_bvh_binary(S, ray, nullptr, oc, closest, h);
+                    fallbacks++;
+                }
+                const bool hit = hit_a | hit_t;
+                if (rng != rng_in) P.pool.misc[slot].x = rng;
                 P.pool.hit[slot] = make_float4(h.t, h.uu, h.vv, 0.0f);
-                P.pool.hid[slot] = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, 0);
-                cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : 4;
-                if (P.prim_type && misc.w == 0u) {           // first query of the item: the primary ray
-                    const uint32_t p = shard_pixel(S.shard, S.W, misc.y);
+                const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
+                P.pool.hid[slot] = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
+                if (P.prim_type && miscw == 0u) {                  // first query of the item: the primary ray
+                    const uint32_t p = shard_pixel(S.shard, S.W, miscy);
                     P.prim_type[p] = hit ? (h.kind == HIT_VOLUME ? 0 : h.kind) : -1;
                     P.prim_index[p] = hit ? (h.kind == HIT_TRI ? (int)S.triangles[h.index].local_id : h.index) : -1;
                     P.prim_t[p] = hit ? h.t : 0.0f;
                 }
+                has = false;
             }
-        }
-        // warp-ballot compaction into the per-class shade queues
-        #pragma unroll
-        for (int k = 0; k < WF_CLASSES; k++) {
-            const uint32_t m = __ballot_sync(0xffffffffu, cls == k);
-            if (m == 0) continue;
-            uint32_t qb = 0;
-            const int leader = __ffs((int)m) - 1;
-            if ((int)lane == leader) qb = atomicAdd(&ctl->n_shade[k], (uint32_t)__popc(m));
-            qb = __shfl_sync(0xffffffffu, qb, leader);
-            if (cls == k) P.q_shade[k][qb + __popc(m & lanemask_lt())] = slot;
+            const int active = __popc(__ballot_sync(0xffffffffu, has));
+            if (active == 0) break;
+            if (!exhausted && active < WF_REFILL_BELOW) break;
         }
     }
+
     if (COUNT) {
         unsigned v[8] = {c.rays, c.nodes, c.tris, c.spheres, c.quads, c.rng, c.samples, c.aborts};
         #pragma unroll
@@ -112,21 +183,11 @@ __global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, Wf
     if (lane == 0 && fallbacks) atomicAdd(&ctl->fallbacks, fallbacks);
 }
 
-// between extend and shade: lay the class queues out back to back, reset the extend queue
-__global__ void k_wf_ctl_mid(WfParams P) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    WfControl* c = P.ctl;
-    uint32_t off = 0;
-    for (int k = 0; k < WF_CLASSES; k++) { c->shade_off[k] = off; off += c->n_shade[k]; }
-    c->shade_off[WF_CLASSES] = off;
-    c->n_extend = 0; c->extend_cursor = 0;
-}
-
-// after shade: reset the shade queues, find frames that completed, advance the ring window
+// after shade: publish the next ray queue, find frames that completed, advance the ring window
 __global__ void k_wf_ctl_end(WfParams P) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     WfControl* c = P.ctl;
-    for (int k = 0; k < WF_CLASSES; k++) c->n_shade[k] = 0;
+    c->n_extend = c->n_next; c->n_next = 0; c->extend_cursor = 0;
     uint32_t n_ready = 0;
     while (c->acc_k + n_ready < c->n_frames && n_ready < P.ring &&
            c->done[(c->acc_k + n_ready) % P.ring] == P.items_per_frame) {
@@ -153,82 +214,105 @@ __device__ __forceinline__ void start_sample(const DeviceScene& S, uint32_t pixe
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
     __shared__ uint32_t s_done[WF_MAX_RING];
+    __shared__ uint32_t s_cnt[8][WF_CLASSES + 1];      // per warp, per class
+    __shared__ int4 s_hid[256];
+    __shared__ uint32_t s_perm[256];
     __shared__ uint32_t s_warp[8];
     __shared__ uint32_t s_base;
     WfControl* ctl = P.ctl;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     if (threadIdx.x < WF_MAX_RING) s_done[threadIdx.x] = 0;
-    __syncthreads();
 
-    const uint32_t total = ctl->shade_off[WF_CLASSES];
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    // ---- material sort inside the block: slot (block base + j) -> thread rank by (class, j) ----
+    const uint32_t block_base = blockIdx.x * blockDim.x;
+    {
+        const uint32_t s0 = block_base + threadIdx.x;
+        int4 hid = make_int4(HIT_NONE, -1, -1, WF_CLS_DEAD);
+        if (s0 < P.pool.capacity) hid = P.pool.hid[s0];
+        s_hid[threadIdx.x] = hid;
+        const int cls = hid.w;
+        uint32_t my_rank_in_warp = 0;
+        #pragma unroll
+        for (int k = 0; k < WF_CLASSES; k++) {
+            const uint32_t m = __ballot_sync(0xffffffffu, cls == k);
+            if (cls == k) my_rank_in_warp = (uint32_t)__popc(m & lanemask_lt());
+            if (lane == 0) s_cnt[warp][k] = (uint32_t)__popc(m);
+        }
+        __syncthreads();
+        // exclusive offset of (class, warp) in class-major order
+        uint32_t off = 0;
+        for (int k = 0; k < cls; k++)
+            for (int w = 0; w < 8; w++) off += s_cnt[w][k];
+        for (uint32_t w = 0; w < warp; w++) off += s_cnt[w][cls];
+        s_perm[off + my_rank_in_warp] = threadIdx.x;
+        __syncthreads();
+    }
+    const uint32_t j = s_perm[threadIdx.x];
+    const uint32_t slot = block_base + j;
+    const int4 hid = s_hid[j];
+    const int cls = hid.w;
+
     const uint32_t npix = (uint32_t)S.W * (uint32_t)S.H;
     const int side = S.K.STRATIFY ? strat_side(S) : 1;
     const uint32_t samples_per_item = S.K.STRATIFY ? (uint32_t)(side * side) : (uint32_t)S.K.NUM_SAMPLES;
 
     bool alive = false, need_work = false, store_pix = false;
-    uint32_t slot = 0, rng = 0, pix_i = 0, frame_k = 0, bounce = 0, scnt = 0;
+    uint32_t rng = 0, pix_i = 0, frame_k = 0, bounce = 0, scnt = 0;
     unsigned n_samples = 0, n_draws = 0;
     Ray ray; ray.o = ray.d = V3s(0.0f);
     v3 thr = V3s(1.0f), acc = V3s(0.0f);
     float4 pix = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 
-    if (t < total) {
-        int cls = 0;
-        while (t >= ctl->shade_off[cls + 1]) cls++;
-        slot = P.q_shade[cls][t - ctl->shade_off[cls]];
+    if (cls == WF_CLS_IDLE) {
+        need_work = true;
+    } else if (cls <= WF_CLS_MISS) {
         bool ended = false;
-        if (cls == 5) {
-            need_work = true;
+        const uint4 misc = P.pool.misc[slot];
+        rng = misc.x; pix_i = misc.y; frame_k = misc.z; bounce = misc.w >> 16; scnt = misc.w & 0xffffu;
+        const float4 t4 = P.pool.thr[slot], a4 = P.pool.acc[slot];
+        thr = V3(t4.x, t4.y, t4.z); acc = V3(a4.x, a4.y, a4.z);
+        if (cls == WF_CLS_MISS) {                             // traceRay.wgsl:12-16
+            acc = acc + V3(0.0f, 1.0f, 1.0f) * thr;
+            ended = true;
         } else {
-            const uint4 misc = P.pool.misc[slot];
-            rng = misc.x; pix_i = misc.y; frame_k = misc.z; bounce = misc.w >> 16; scnt = misc.w & 0xffffu;
-            const float4 t4 = P.pool.thr[slot], a4 = P.pool.acc[slot];
-            thr = V3(t4.x, t4.y, t4.z); acc = V3(a4.x, a4.y, a4.z);
-            if (cls == 4) {                                   // miss: traceRay.wgsl:12-16
-                acc = acc + V3(0.0f, 1.0f, 1.0f) * thr;
-                ended = true;
+            const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot], h4 = P.pool.hit[slot];
+            ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
+            HitLite h; h.t = h4.x; h.uu = h4.y; h.vv = h4.z; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
+            ObjRayCache oc; oc.reset();
+            ShadeState st;
+            st.p = st.n = st.unit_w = st.u = st.v = V3s(0.0f);
+            st.front_face = false; st.skip_pdf = false; st.doSpecular = 0.0f;
+            st.skip_ray.o = st.skip_ray.d = V3s(0.0f);
+            finalize_hit(S, ray, h, oc, st);
+            const Material m = S.materials[h.mat_id];
+            bool early;
+            const bool cont = bounce_update(S, m, (int)bounce, ray, st, rng, n_draws, acc, thr, early);
+            bounce++;
+            ended = !cont || (int)bounce >= S.K.MAX_BOUNCES;           // `for (i < MAX_BOUNCES)`
+            alive = !ended;
+        }
+        if (ended) {
+            // the sample's ray_color() value is `acc`: shootRay.wgsl:25,42 `pixColor += ray_color(ray)`
+            pix = P.pool.pix[slot];
+            pix.x = fa(pix.x, acc.x); pix.y = fa(pix.y, acc.y); pix.z = fa(pix.z, acc.z); pix.w += 1.0f;
+            scnt++;
+            const uint32_t pixel = shard_pixel(S.shard, S.W, pix_i);
+            if (scnt < samples_per_item) {
+                start_sample(S, pixel, scnt, side, rng, ray);              // next sample, same RNG stream
+                n_draws += 2; n_samples++;
+                thr = V3s(1.0f); acc = V3s(0.0f); bounce = 0;
+                alive = true; store_pix = true;
             } else {
-                const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot], h4 = P.pool.hit[slot];
-                const int4 hid = P.pool.hid[slot];
-                ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
-                HitLite h; h.t = h4.x; h.uu = h4.y; h.vv = h4.z; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
-                ObjRayCache oc; oc.reset();
-                ShadeState st;
-                st.p = st.n = st.unit_w = st.u = st.v = V3s(0.0f);
-                st.front_face = false; st.skip_pdf = false; st.doSpecular = 0.0f;
-                st.skip_ray.o = st.skip_ray.d = V3s(0.0f);
-                finalize_hit(S, ray, h, oc, st);
-                const Material m = S.materials[h.mat_id];
-                bool early;
-                const bool cont = bounce_update(S, m, (int)bounce, ray, st, rng, n_draws, acc, thr, early);
-                bounce++;
-                ended = !cont || (int)bounce >= S.K.MAX_BOUNCES;       // `for (i < MAX_BOUNCES)`
-                alive = !ended;
-            }
-            if (ended) {
-                // the sample's ray_color() value is `acc`: shootRay.wgsl:25,42 `pixColor += ray_color(ray)`
-                pix = P.pool.pix[slot];
-                pix.x = fa(pix.x, acc.x); pix.y = fa(pix.y, acc.y); pix.z = fa(pix.z, acc.z); pix.w += 1.0f;
-                scnt++;
-                const uint32_t pixel = shard_pixel(S.shard, S.W, pix_i);
-                if (scnt < samples_per_item) {
-                    start_sample(S, pixel, scnt, side, rng, ray);          // next sample, same RNG stream
-                    n_draws += 2; n_samples++;
-                    thr = V3s(1.0f); acc = V3s(0.0f); bounce = 0;
-                    alive = true; store_pix = true;
-                } else {
-                    const float div = S.K.STRATIFY ? pix.w : (float)S.K.NUM_SAMPLES;
-                    P.stage[(size_t)(frame_k % P.ring) * npix + pixel] = make_float4(fd(pix.x, div), fd(pix.y, div), fd(pix.z, div), 1.0f);
-                    atomicAdd(&s_done[frame_k % P.ring], 1u);
-                    need_work = true;
-                }
+                const float div = S.K.STRATIFY ? pix.w : (float)S.K.NUM_SAMPLES;
+                P.stage[(size_t)(frame_k % P.ring) * npix + pixel] = make_float4(fd(pix.x, div), fd(pix.y, div), fd(pix.z, div), 1.0f);
+                atomicAdd(&s_done[frame_k % P.ring], 1u);
+                need_work = true;
             }
         }
     }
 
     // ---- generate: pull the next (frame, pixel) work items, warp-aggregated ----
-    bool requeue_idle = false;
+    int new_cls = WF_CLS_DEAD;
     {
         const uint32_t m = __ballot_sync(0xffffffffu, need_work);
         if (m) {
@@ -247,12 +331,13 @@ __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
             more_later = __shfl_sync(0xffffffffu, more_later, leader);
             if (need_work) {
                 const uint32_t r = (uint32_t)__popc(m & lanemask_lt());
+                new_cls = more_later ? WF_CLS_IDLE : WF_CLS_DEAD;
                 if (r < granted) {
                     const unsigned long long w = old + r;
                     frame_k = (uint32_t)(w / P.items_per_frame);
                     pix_i = (uint32_t)(w - (unsigned long long)frame_k * P.items_per_frame);
                     const uint32_t pixel = shard_pixel(S.shard, S.W, pix_i);
-                    uint32_t lim_pix = npix < S.shard.pixel_limit ? npix : S.shard.pixel_limit;
+                    const uint32_t lim_pix = npix < S.shard.pixel_limit ? npix : S.shard.pixel_limit;
                     if (pixel < lim_pix) {
                         const float frame = (float)(P.frame0 + (int)frame_k * P.frame_stride);
                         rng = pixel_seed(pixel, frame);
@@ -264,10 +349,8 @@ __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
                         alive = true; store_pix = true;
                     } else {
                         atomicAdd(&s_done[frame_k % P.ring], 1u);      // tile tail past the image: nothing to render
-                        requeue_idle = more_later != 0;
+                        new_cls = WF_CLS_IDLE;                         // try again next iteration
                     }
-                } else {
-                    requeue_idle = more_later != 0;                    // window is full: wait for a frame to retire
                 }
             }
         }
@@ -280,23 +363,21 @@ __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
         P.pool.acc[slot] = make_float4(acc.x, acc.y, acc.z, 0.0f);
         P.pool.misc[slot] = make_uint4(rng, pix_i, frame_k, (bounce << 16) | (scnt & 0xffffu));
         if (store_pix) P.pool.pix[slot] = pix;
-        P.pool.hid[slot].x = HIT_NONE;
-    } else if (requeue_idle) {
-        P.pool.hid[slot].x = WF_KIND_IDLE;
+    } else if (cls <= WF_CLS_IDLE && new_cls != cls) {
+        P.pool.hid[slot].w = new_cls;               // idle (waiting for the window) or dead (no work left)
     }
 
-    // ---- compact: survivors (and waiting slots) into the next extend queue, one atomic per block ----
-    const bool push = alive || requeue_idle;
-    const uint32_t m = __ballot_sync(0xffffffffu, push);
+    // ---- compact: live rays into the next ray queue, one atomic per block ----
+    const uint32_t m = __ballot_sync(0xffffffffu, alive);
     if (lane == 0) s_warp[warp] = (uint32_t)__popc(m);
     __syncthreads();
     if (threadIdx.x == 0) {
         uint32_t sum = 0;
         for (int k = 0; k < 8; k++) { const uint32_t v = s_warp[k]; s_warp[k] = sum; sum += v; }
-        s_base = sum ? atomicAdd(&ctl->n_extend, sum) : 0u;
+        s_base = sum ? atomicAdd(&ctl->n_next, sum) : 0u;
     }
     __syncthreads();
-    if (push) P.q_extend[s_base + s_warp[warp] + (uint32_t)__popc(m & lanemask_lt())] = slot;
+    if (alive) P.q_extend[s_base + s_warp[warp] + (uint32_t)__popc(m & lanemask_lt())] = slot;
     if (threadIdx.x < WF_MAX_RING && s_done[threadIdx.x]) atomicAdd(&ctl->done[threadIdx.x], s_done[threadIdx.x]);
 
     if (COUNT) {
@@ -333,12 +414,21 @@ void wf_launch_init(const WfParams& P, uint32_t n_frames, cudaStream_t stream) {
 
 void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
                          cudaStream_t stream, cudaEvent_t* ev) {
-    const unsigned extend_blocks = 148u * 8u;                // persistent: 8 CTAs of 4 warps per SM
+    // persistent grid: exactly as many CTAs as fit on the device (SM count x resident CTAs per SM)
+    static unsigned extend_blocks_cached[2] = {0, 0};
+    unsigned& extend_blocks = extend_blocks_cached[S.counters ? 1 : 0];
+    if (!extend_blocks) {
+        int dev = 0, sms = 148, per_sm = 4;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (S.counters) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_extend<true>, 128, 0);
+        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_extend<false>, 128, 0);
+        extend_blocks = (unsigned)(sms * (per_sm > 0 ? per_sm : 1));
+    }
     if (ev) cudaEventRecord(ev[0], stream);
     if (S.counters) k_wf_extend<true><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     if (ev) cudaEventRecord(ev[1], stream);
-    k_wf_ctl_mid<<<1, 32, 0, stream>>>(P);
     const unsigned shade_blocks = (P.pool.capacity + 255u) / 256u;
     if (S.counters) k_wf_shade<true><<<shade_blocks, 256, 0, stream>>>(S, P);
     else k_wf_shade<false><<<shade_blocks, 256, 0, stream>>>(S, P);

@@ -11,8 +11,13 @@
 namespace wg {
 
 #define WF_MAX_RING 64
-#define WF_CLASSES 6            // 0..3 material_type of the hit, 4 miss, 5 idle (slot waiting for work)
-#define WF_KIND_IDLE (-2)
+// slot status / shade class, kept in hid.w: 0..3 = material_type of the hit to shade, 4 = miss to
+// shade, 5 = idle (no path; waiting for the ring window to release work), 6 = dead (no path, no
+// work left)
+#define WF_CLS_MISS 4
+#define WF_CLS_IDLE 5
+#define WF_CLS_DEAD 6
+#define WF_CLASSES 7
 
 // One path per slot, structure-of-arrays, 16-byte elements (LDG.128 / STG.128).
 struct PathPool {
@@ -22,7 +27,7 @@ struct PathPool {
     float4* acc;     // accumulated radiance of the current sample .xyz
     float4* pix;     // pixColor of the (pixel, frame) so far .xyz, .w = samples taken (stratified divisor)
     float4* hit;     // t, uu, vv of the last closest-hit query
-    int4*   hid;     // kind (HitKind / WF_KIND_IDLE), index, mat_id, -
+    int4*   hid;     // kind (HitKind), index, mat_id, shade class (WF_CLS_*)
     uint4*  misc;    // rng state, shard-local pixel i, frame ordinal k, (bounce << 16) | sample counter
     uint32_t capacity;
 };
@@ -31,11 +36,9 @@ struct WfControl {
     unsigned long long next_work;      // next (frame ordinal, pixel) item to hand out
     unsigned long long work_limit;     // items below this may start (ring window)
     unsigned long long total_work;
-    uint32_t n_extend;                 // rays queued for the extend stage
+    uint32_t n_extend;                 // rays queued for the extend stage of this iteration
     uint32_t extend_cursor;            // persistent-warp fetch cursor
-    uint32_t n_shade[WF_CLASSES];
-    uint32_t shade_off[WF_CLASSES + 1];
-    uint32_t shade_cursor;
+    uint32_t n_next;                   // rays compacted by shade for the next iteration
     uint32_t done[WF_MAX_RING];        // finished items per ring slot
     uint32_t acc_k;                    // next frame ordinal to fold into binding 3
     uint32_t ready_first, n_ready;     // frames the accumulate pass folds this iteration
@@ -48,8 +51,7 @@ struct WfControl {
 struct WfParams {
     PathPool pool;
     WfControl* ctl;
-    uint32_t* q_extend;                // slot ids, capacity entries
-    uint32_t* q_shade[WF_CLASSES];     // slot ids per class, capacity entries each
+    uint32_t* q_extend;                // slot ids of live rays, compacted by shade (capacity entries)
     float4* stage;                     // ring x W*H: (pixColor, 1)
     uint32_t ring;                     // frames in flight
     uint32_t items_per_frame;          // shard.n_pixels
@@ -58,12 +60,13 @@ struct WfParams {
     int* prim_type; int* prim_index; float* prim_t;
 };
 
+
 // wavefront.cu
 void wf_launch_init(const WfParams& P, uint32_t n_frames, cudaStream_t stream);
 // ev: optional 4 events recorded before extend, after extend, after shade, after accumulate
 void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
                          cudaStream_t stream, cudaEvent_t* ev = nullptr);
-#define WF_LAUNCHES_PER_ITERATION 5
+#define WF_LAUNCHES_PER_ITERATION 4
 void launch_trace_rays_wide(const DeviceScene& S, const WideBvh& WB, int n, const float* rays, const uint32_t* seeds,
                             int* out_type, int* out_index, float* out_t, uint32_t* fallbacks, cudaStream_t stream);
 
