@@ -26,7 +26,7 @@
 namespace wg {
 
 #ifndef WF_REFILL_BELOW
-#define WF_REFILL_BELOW 22      // refill the warp when fewer lanes than this still traverse
+#define WF_REFILL_BELOW 26      // refill the warp when fewer lanes than this still traverse
 #endif
 
 __device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
@@ -47,7 +47,36 @@ __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
     }
 }
 
+// first closest-hit query of a (pixel, frame) item -> parity probe arrays
+__device__ __forceinline__ void write_probe(const DeviceScene& S, const WfParams& P, uint32_t pix_i, bool hit, const HitLite& h) {
+    const uint32_t p = shard_pixel(S.shard, S.W, pix_i);
+    P.prim_type[p] = hit ? (h.kind == HIT_VOLUME ? 0 : h.kind) : -1;
+    P.prim_index[p] = hit ? (h.kind == HIT_TRI ? (int)S.triangles[h.index].local_id : h.index) : -1;
+    P.prim_t[p] = hit ? h.t : 0.0f;
+}
+
+// Conservative test of a ray against the root box of the BVH over (0, closest]: rays that fail it
+// cannot hit any triangle and never enter the extend queue.
+__device__ __forceinline__ bool root_box_hit(const DeviceScene& S, const Ray& ray, float closest) {
+    const WideRay wr = make_wide_ray(ray);
+    const float4 a = __ldg(reinterpret_cast<const float4*>(S.bvh)), b = __ldg(reinterpret_cast<const float4*>(S.bvh) + 1);
+    const float x0 = (a.x - ray.o.x) * wr.idx, x1 = (b.x - ray.o.x) * wr.idx;
+    const float y0 = (a.y - ray.o.y) * wr.idy, y1 = (b.y - ray.o.y) * wr.idy;
+    const float z0 = (a.z - ray.o.z) * wr.idz, z1 = (b.z - ray.o.z) * wr.idz;
+    const float tlo = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+    const float thi = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), closest));
+    return tlo * 0.999998f <= thi * 1.000002f;
+}
+
 // ---------------------------------------------------------------- extend
+// The sphere/quad part of hitScene (hitRay.wgsl:6-40) was already evaluated by the shade stage
+// when it produced the ray (all lanes in lock step there); this kernel walks the wide BVH.
+// Node visits and triangle tests run as separate warp phases: a lane that found candidate
+// triangles parks them until TRI_BATCH lanes have some (or nobody has node work left).
+#ifndef WF_TRI_BATCH
+#define WF_TRI_BATCH 8
+#endif
+
 template <bool COUNT>
 __global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, WfParams P) {
     WfControl* ctl = P.ctl;
@@ -56,17 +85,17 @@ __global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, Wf
     Counts c = {0, 0, 0, 0, 0, 0, 0, 0};
     unsigned fallbacks = 0;
 
-    // per-lane ray + traversal state
     bool has = false, exhausted = (n == 0);
-    uint32_t slot = 0, rng = 0, rng_in = 0, miscw = 0, miscy = 0;
+    uint32_t slot = 0;
     Ray ray; ray.o = ray.d = V3s(0.0f);
     WideRay wr; wr.idx = wr.idy = wr.idz = 0.0f; wr.octinv = 0;
     ObjRayCache oc; oc.reset();
     HitLite h, h0;
     h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1; h0 = h;
     float closest = WGPT_MAX_FLOAT, c0 = WGPT_MAX_FLOAT;
-    bool hit_a = false, hit_t = false, ambiguous = false;
+    bool hit_t = false, ambiguous = false;
     uint2 G = make_uint2(0u, 0u);
+    uint32_t tm = 0, tri_base = 0;               // parked candidate triangles of the last node visited
     uint2 stack[WIDE_STACK];
     int sp = 0;
 
@@ -84,20 +113,17 @@ __global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, Wf
                     const uint32_t idx = base + (uint32_t)__popc(m & lanemask_lt());
                     if (idx < n) {
                         slot = P.q_extend[idx];
-                        const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot];
-                        const uint4 misc = P.pool.misc[slot];
+                        const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot], h4 = P.pool.hit[slot];
+                        const int4 hid = P.pool.hid[slot];
                         ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
-                        rng = rng_in = misc.x; miscy = misc.y; miscw = misc.w;
-                        // spheres + quads (hitRay.wgsl:6-40), then set the BVH walk up
-                        closest = WGPT_MAX_FLOAT;
-                        h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1;
-                        if (COUNT) c.rays++;
+                        // sphere/quad result carried in by shade
+                        h0.t = h4.x; h0.uu = 0.0f; h0.vv = 0.0f; h0.kind = hid.x; h0.index = hid.y; h0.mat_id = hid.z;
+                        c0 = hid.x == HIT_NONE ? WGPT_MAX_FLOAT : h4.x;
+                        h = h0; closest = c0;
                         oc.reset();
-                        hit_a = hit_analytic(S, ray, rng, COUNT ? &c : nullptr, closest, h);
-                        h0 = h; c0 = closest;
-                        hit_t = false; ambiguous = false; sp = 0;
+                        hit_t = false; ambiguous = false; sp = 0; tm = 0;
                         wr = make_wide_ray(ray);
-                        G = WB.n_nodes ? make_uint2(0u, 0x80000000u) : make_uint2(0u, 0u);
+                        G = make_uint2(0u, 0x80000000u);
                         has = true;
                     }
                 }
@@ -106,61 +132,64 @@ __global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, Wf
         }
         if (__ballot_sync(0xffffffffu, has) == 0) break;        // queue drained and every lane finished
 
-        // ---- traverse: one wide-node visit per step for every lane that still has one pending ----
         while (true) {
-            if (has && (G.y & 0xff000000u)) {
+            if (has && tm == 0u && !(G.y & 0xff000000u) && sp > 0) G = stack[--sp];
+            // ---- node phase: one wide-node visit for every lane with a node pending and no parked triangles ----
+            const bool node_work = has && tm == 0u && (G.y & 0xff000000u);
+            if (node_work) {
                 const uint32_t bit = 31u - (uint32_t)__clz((int)(G.y & 0xff000000u));
                 const uint32_t hits_imask = G.y;
-                bool abort_walk = false;
                 G.y &= ~(1u << bit);
+                bool overflow = false;
                 if (G.y & 0xff000000u) {
-                    if (sp >= WIDE_STACK) abort_walk = true;        // deeper than the wide stack: reference walk decides
+                    if (sp >= WIDE_STACK) overflow = true;          // deeper than the wide stack: reference walk decides
                     else stack[sp++] = G;
                 }
-                if (!abort_walk) {
+                if (overflow) { ambiguous = true; G.y = 0u; sp = 0; }
+                else {
                     const uint32_t sl = (bit - 24u) ^ wr.octinv;
                     const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << sl) & 0xffu);
-                    uint32_t child_base, tri_base, imask;
+                    uint32_t child_base, imask;
                     if (COUNT) c.nodes++;
                     const uint32_t hm = wide_node_hits(WB.nodes, G.x + rel, ray, wr, closest, child_base, tri_base, imask);
                     G = make_uint2(child_base, (hm & 0xff000000u) | imask);
-                    uint32_t tm = hm & 0x00ffffffu;
-                    while (tm) {
-                        const int b = __ffs((int)tm) - 1;
-                        tm &= tm - 1u;
-                        const float4* t = &WB.tris[3 * (size_t)(tri_base + (uint32_t)b)];
-                        const float4 A = __ldg(&t[0]), B = __ldg(&t[1]), C = __ldg(&t[2]);
-                        oc.fetch(S, __float_as_int(B.w), ray);
-                        float dst, uu, vv;
-                        if (COUNT) c.tris++;
-                        if (tri_test(V3(A.x, A.y, A.z), V3(B.x, B.y, B.z), V3(C.x, C.y, C.z), oc.oray, WGPT_RAY_TMIN, closest, dst, uu, vv)) {
-                            if (hit_t && dst == closest) abort_walk = true;      // equal-distance triangles: visit order decides
-                            hit_t = true; closest = dst;
-                            h.t = dst; h.kind = HIT_TRI; h.index = __float_as_int(A.w); h.uu = uu; h.vv = vv;
-                            h.mat_id = oc.m.material_id;
-                        }
+                    tm = hm & 0x00ffffffu;
+                }
+            }
+            // ---- triangle phase: one parked triangle per lane, once enough lanes have one ----
+            const int n_tri = __popc(__ballot_sync(0xffffffffu, has && tm != 0u));
+            const int n_node = __popc(__ballot_sync(0xffffffffu, has && tm == 0u && ((G.y & 0xff000000u) || sp > 0)));
+            if (n_tri >= WF_TRI_BATCH || (n_tri > 0 && n_node == 0)) {
+                if (has && tm != 0u) {
+                    const int b = __ffs((int)tm) - 1;
+                    tm &= tm - 1u;
+                    const float4* t = &WB.tris[3 * (size_t)(tri_base + (uint32_t)b)];
+                    const float4 A = __ldg(&t[0]), B = __ldg(&t[1]), C = __ldg(&t[2]);
+                    oc.fetch(S, __float_as_int(B.w), ray);
+                    float dst, uu, vv;
+                    if (COUNT) c.tris++;
+                    if (tri_test(V3(A.x, A.y, A.z), V3(B.x, B.y, B.z), V3(C.x, C.y, C.z), oc.oray, WGPT_RAY_TMIN, closest, dst, uu, vv)) {
+                        if (hit_t && dst == closest) { ambiguous = true; G.y = 0u; sp = 0; tm = 0u; }   // equal-distance triangles: visit order decides
+                        hit_t = true; closest = dst;
+                        h.t = dst; h.kind = HIT_TRI; h.index = __float_as_int(A.w); h.uu = uu; h.vv = vv;
+                        h.mat_id = oc.m.material_id;
                     }
                 }
-                if (abort_walk) { ambiguous = true; G.y = 0u; sp = 0; }
-                else if (!(G.y & 0xff000000u) && sp > 0) G = stack[--sp];
             }
-            // lanes whose walk is over write their result back and free the lane
-            if (has && !(G.y & 0xff000000u)) {
+            // ---- lanes whose walk is over write their result back and free the lane ----
+            if (has && tm == 0u && !(G.y & 0xff000000u) && sp == 0) {
                 if (ambiguous) {                                   // re-derive in reference order
                     h = h0; closest = c0;
                     hit_t = hit_bvh_binary(S, ray, nullptr, oc, closest, h);
                     fallbacks++;
                 }
-                const bool hit = hit_a | hit_t;
-                if (rng != rng_in) P.pool.misc[slot].x = rng;
+                const bool hit = (h0.kind != HIT_NONE) | hit_t;
                 P.pool.hit[slot] = make_float4(h.t, h.uu, h.vv, 0.0f);
                 const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
                 P.pool.hid[slot] = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
-                if (P.prim_type && miscw == 0u) {                  // first query of the item: the primary ray
-                    const uint32_t p = shard_pixel(S.shard, S.W, miscy);
-                    P.prim_type[p] = hit ? (h.kind == HIT_VOLUME ? 0 : h.kind) : -1;
-                    P.prim_index[p] = hit ? (h.kind == HIT_TRI ? (int)S.triangles[h.index].local_id : h.index) : -1;
-                    P.prim_t[p] = hit ? h.t : 0.0f;
+                if (P.prim_type) {
+                    const uint4 misc = P.pool.misc[slot];
+                    if (misc.w == 0u) write_probe(S, P, misc.y, hit, h);     // first query of the item: the primary ray
                 }
                 has = false;
             }
@@ -259,6 +288,7 @@ __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
     bool alive = false, need_work = false, store_pix = false;
     uint32_t rng = 0, pix_i = 0, frame_k = 0, bounce = 0, scnt = 0;
     unsigned n_samples = 0, n_draws = 0;
+    Counts cnt = {0, 0, 0, 0, 0, 0, 0, 0};
     Ray ray; ray.o = ray.d = V3s(0.0f);
     v3 thr = V3s(1.0f), acc = V3s(0.0f);
     float4 pix = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
@@ -356,19 +386,32 @@ __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
         }
     }
 
+    // ---- the new ray's sphere/quad part of hitScene (hitRay.wgsl:6-40) runs here, where all lanes are
+    // in lock step; only rays that can still reach a triangle (root box within reach) go to extend ----
+    bool trace = false;
     if (alive) {
+        HitLite h; h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1;
+        float closest = WGPT_MAX_FLOAT;
+        if (COUNT) cnt.rays++;
+        const bool hit_a = hit_analytic(S, ray, rng, COUNT ? &cnt : nullptr, closest, h);
+        trace = S.NUM_AABB > 0 && root_box_hit(S, ray, closest);
+        const int ncls = trace ? WF_CLS_TRACE : (hit_a ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS);
+        const uint32_t miscw = (bounce << 16) | (scnt & 0xffffu);
         P.pool.ro[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, 0.0f);
         P.pool.rd[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.0f);
         P.pool.thr[slot] = make_float4(thr.x, thr.y, thr.z, 0.0f);
         P.pool.acc[slot] = make_float4(acc.x, acc.y, acc.z, 0.0f);
-        P.pool.misc[slot] = make_uint4(rng, pix_i, frame_k, (bounce << 16) | (scnt & 0xffffu));
+        P.pool.misc[slot] = make_uint4(rng, pix_i, frame_k, miscw);
         if (store_pix) P.pool.pix[slot] = pix;
+        P.pool.hit[slot] = make_float4(h.t, 0.0f, 0.0f, 0.0f);
+        P.pool.hid[slot] = make_int4(hit_a ? h.kind : (int)HIT_NONE, h.index, h.mat_id, ncls);
+        if (!trace && P.prim_type && miscw == 0u) write_probe(S, P, pix_i, hit_a, h);
     } else if (cls <= WF_CLS_IDLE && new_cls != cls) {
         P.pool.hid[slot].w = new_cls;               // idle (waiting for the window) or dead (no work left)
     }
 
-    // ---- compact: live rays into the next ray queue, one atomic per block ----
-    const uint32_t m = __ballot_sync(0xffffffffu, alive);
+    // ---- compact: rays that need the BVH into the next ray queue, one atomic per block ----
+    const uint32_t m = __ballot_sync(0xffffffffu, trace);
     if (lane == 0) s_warp[warp] = (uint32_t)__popc(m);
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -377,13 +420,18 @@ __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
         s_base = sum ? atomicAdd(&ctl->n_next, sum) : 0u;
     }
     __syncthreads();
-    if (alive) P.q_extend[s_base + s_warp[warp] + (uint32_t)__popc(m & lanemask_lt())] = slot;
+    if (trace) P.q_extend[s_base + s_warp[warp] + (uint32_t)__popc(m & lanemask_lt())] = slot;
     if (threadIdx.x < WF_MAX_RING && s_done[threadIdx.x]) atomicAdd(&ctl->done[threadIdx.x], s_done[threadIdx.x]);
 
     if (COUNT) {
-        unsigned long long a = n_samples, b = n_draws;
-        for (int o = 16; o > 0; o >>= 1) { a += __shfl_down_sync(0xffffffffu, a, o); b += __shfl_down_sync(0xffffffffu, b, o); }
-        if (lane == 0) { if (a) atomicAdd(&S.counters[6], a); if (b) atomicAdd(&S.counters[5], b); }
+        cnt.samples += n_samples; cnt.rng += n_draws;
+        unsigned v[8] = {cnt.rays, cnt.nodes, cnt.tris, cnt.spheres, cnt.quads, cnt.rng, cnt.samples, cnt.aborts};
+        #pragma unroll
+        for (int k = 0; k < 8; k++) {
+            unsigned long long x = v[k];
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+            if (lane == 0 && x) atomicAdd(&S.counters[k], x);
+        }
     }
 }
 

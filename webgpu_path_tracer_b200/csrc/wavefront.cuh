@@ -13,11 +13,12 @@ namespace wg {
 #define WF_MAX_RING 64
 // slot status / shade class, kept in hid.w: 0..3 = material_type of the hit to shade, 4 = miss to
 // shade, 5 = idle (no path; waiting for the ring window to release work), 6 = dead (no path, no
-// work left)
+// work left), 7 = in the extend queue
 #define WF_CLS_MISS 4
 #define WF_CLS_IDLE 5
 #define WF_CLS_DEAD 6
-#define WF_CLASSES 7
+#define WF_CLS_TRACE 7      // ray queued for the extend stage (which overwrites the class)
+#define WF_CLASSES 8
 
 // One path per slot, structure-of-arrays, 16-byte elements (LDG.128 / STG.128).
 struct PathPool {
