@@ -51,7 +51,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("WGPT_LIB") or LIB_PATH      # WGPT_LIB: developer A/B builds
     if not os.path.exists(p):
         raise WgptError("libwgpt.so not built (%s): run `python -c 'import __graft_entry__ as g; g.build()'`; "
                         "there is no CPU fallback" % p)

@@ -8,6 +8,7 @@
 // common.wgsl:219 accepts dst == tmax); such rays -- and rays whose traversal stack would
 // overflow -- are flagged and re-traced with the reference-order binary walk (trace_binary.cuh).
 #pragma once
+#include <cuda_fp16.h>
 #include "intersect.cuh"
 #include "trace_binary.cuh"
 #include "wide_bvh.cuh"
@@ -32,61 +33,88 @@ __device__ __forceinline__ WideRay make_wide_ray(const Ray& r) {
     return w;
 }
 
-__device__ __forceinline__ uint32_t byte_of(uint32_t lo, uint32_t hi, int s) {
-    return ((s < 4 ? lo : hi) >> ((s & 3) * 8)) & 0xffu;
+// Octant permutation table: lut[c * 256 + H] has bit (s ^ c) set for every bit s of H, so a hit
+// byte in slot order becomes a byte in visit-priority order (highest bit = nearest octant first)
+// with one shared-memory load.  Every kernel that traverses fills its own copy once per block.
+#define WIDE_LUT_BYTES 2048
+__device__ __forceinline__ void wide_lut_init(unsigned char* lut) {
+    for (uint32_t i = threadIdx.x; i < WIDE_LUT_BYTES; i += blockDim.x) {
+        const uint32_t c = i >> 8, H = i & 255u;
+        uint32_t r = 0;
+        #pragma unroll
+        for (uint32_t b = 0; b < 8; b++) r |= ((H >> b) & 1u) << (b ^ c);
+        lut[i] = (unsigned char)r;
+    }
+    __syncthreads();
 }
 
-// Intersects the 8 children of one wide node; returns the hit mask (bits 24..31: inner children
-// in octant order, bits 0..23: triangles of the leaf children) and the node's q1 words.
+// Two quantised plane bytes -> two floats (byte * 2^-24) without the conversion unit: PRMT builds
+// the half2 whose lanes are the SUBNORMAL halves 0x00bb (= b * 2^-24 exactly) and the widening
+// HADD2.F32 runs on the FMA pipe (I2F.U8 costs 8 issue cycles per warp on sm_100a, measured; 48
+// of them per node visit made the conversion unit the bottleneck of the whole traversal).  The
+// 2^24 is folded into the per-node scale.
+__device__ __forceinline__ void cvt2(uint32_t w, uint32_t sel, float& f0, float& f1) {
+    const uint32_t p = __byte_perm(w, 0u, sel);
+    const __half2 h = *reinterpret_cast<const __half2*>(&p);
+    f0 = __low2float(h); f1 = __high2float(h);
+}
+
+// Intersects the 8 children of one wide node; returns the hit byte in SLOT order (bit s = the box
+// in slot s is hit over (0, closest]); empty slots never report.
 __device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nodes, uint32_t ni, const Ray& ray,
                                                    const WideRay& wr, float closest, uint32_t& child_base,
-                                                   uint32_t& tri_base, uint32_t& imask) {
+                                                   uint32_t& tri_base, uint32_t& imask, uint32_t& lmask) {
     const uint4 n0 = __ldg(&nodes[5 * (size_t)ni]);
     const uint4 n1 = __ldg(&nodes[5 * (size_t)ni + 1]);
     const uint4 n2 = __ldg(&nodes[5 * (size_t)ni + 2]);
     const uint4 n3 = __ldg(&nodes[5 * (size_t)ni + 3]);
     const uint4 n4 = __ldg(&nodes[5 * (size_t)ni + 4]);
-    child_base = n1.x; tri_base = n1.y; imask = n0.w >> 24;
-    const float adjx = __uint_as_float((n0.w & 0xffu) << 23) * wr.idx;
-    const float adjy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * wr.idy;
-    const float adjz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * wr.idz;
+    child_base = n1.x; tri_base = n1.y; imask = n0.w >> 24; lmask = n1.z & 0xffu;
+    // scale = 2^(e-127) * 2^24 (the subnormal-half conversion yields byte * 2^-24)
+    const float adjx = __uint_as_float(((n0.w & 0xffu) + 24u) << 23) * wr.idx;
+    const float adjy = __uint_as_float((((n0.w >> 8) & 0xffu) + 24u) << 23) * wr.idy;
+    const float adjz = __uint_as_float((((n0.w >> 16) & 0xffu) + 24u) << 23) * wr.idz;
     const float ox = (__uint_as_float(n0.x) - ray.o.x) * wr.idx;
     const float oy = (__uint_as_float(n0.y) - ray.o.y) * wr.idy;
     const float oz = (__uint_as_float(n0.z) - ray.o.z) * wr.idz;
-    // near / far planes by direction sign
+    // near / far plane words by direction sign; [0] = slots 0..3, [1] = slots 4..7
     const bool px = (wr.octinv & 4u) != 0, py = (wr.octinv & 2u) != 0, pz = (wr.octinv & 1u) != 0;
-    const uint32_t nxa = px ? n2.x : n3.z, nxb = px ? n2.y : n3.w, fxa = px ? n3.z : n2.x, fxb = px ? n3.w : n2.y;
-    const uint32_t nya = py ? n2.z : n4.x, nyb = py ? n2.w : n4.y, fya = py ? n4.x : n2.z, fyb = py ? n4.y : n2.w;
-    const uint32_t nza = pz ? n3.x : n4.z, nzb = pz ? n3.y : n4.w, fza = pz ? n4.z : n3.x, fzb = pz ? n4.w : n3.y;
+    const uint32_t nx[2] = {px ? n2.x : n3.z, px ? n2.y : n3.w}, fx[2] = {px ? n3.z : n2.x, px ? n3.w : n2.y};
+    const uint32_t ny[2] = {py ? n2.z : n4.x, py ? n2.w : n4.y}, fy[2] = {py ? n4.x : n2.z, py ? n4.y : n2.w};
+    const uint32_t nz[2] = {pz ? n3.x : n4.z, pz ? n3.y : n4.w}, fz[2] = {pz ? n4.z : n3.x, pz ? n4.w : n3.y};
     const float far_cap = closest * 1.000002f;
-    uint32_t hitmask = 0;
+    // Straight-line code for all 8 slots (no divergence inside a node).  The sign of
+    // min(thi, far) - tlo is the MISS flag; a funnel shift collects the flags, slot 7 first, so
+    // slot s ends up in bit s.
+    uint32_t miss = 0;
     #pragma unroll
-    for (int s = 0; s < 8; s++) {
-        const uint32_t m = byte_of(n1.z, n1.w, s);
-        const uint32_t child_bits = m >> 5;
-        if (child_bits == 0) continue;
-        const float tlx = fmaf((float)byte_of(nxa, nxb, s), adjx, ox), thx = fmaf((float)byte_of(fxa, fxb, s), adjx, ox);
-        const float tly = fmaf((float)byte_of(nya, nyb, s), adjy, oy), thy = fmaf((float)byte_of(fya, fyb, s), adjy, oy);
-        const float tlz = fmaf((float)byte_of(nza, nzb, s), adjz, oz), thz = fmaf((float)byte_of(fza, fzb, s), adjz, oz);
-        const float tlo = fmaxf(fmaxf(tlx, tly), fmaxf(tlz, 0.0f));
-        const float thi = fminf(fminf(thx, thy), thz) * 1.000002f;
-        if (tlo <= fminf(thi, far_cap)) {
-            const bool inner = (m & 0x18u) == 0x18u;
-            const uint32_t bit = inner ? (24u + ((m & 7u) ^ wr.octinv)) : (m & 31u);
-            hitmask |= child_bits << bit;
+    for (int pr = 3; pr >= 0; pr--) {
+        const int w = pr >> 1;
+        const uint32_t sel = (pr & 1) ? 0x4342u : 0x4140u;
+        float tlx[2], thx[2], tly[2], thy[2], tlz[2], thz[2];
+        cvt2(nx[w], sel, tlx[0], tlx[1]); cvt2(fx[w], sel, thx[0], thx[1]);
+        cvt2(ny[w], sel, tly[0], tly[1]); cvt2(fy[w], sel, thy[0], thy[1]);
+        cvt2(nz[w], sel, tlz[0], tlz[1]); cvt2(fz[w], sel, thz[0], thz[1]);
+        #pragma unroll
+        for (int k = 1; k >= 0; k--) {
+            const float tlo = fmaxf(fmaxf(fmaf(tlx[k], adjx, ox), fmaf(tly[k], adjy, oy)), fmaxf(fmaf(tlz[k], adjz, oz), 0.0f));
+            const float thi = fminf(fminf(fmaf(thx[k], adjx, ox), fmaf(thy[k], adjy, oy)), fmaf(thz[k], adjz, oz)) * 1.000002f;
+            const float d = fminf(thi, far_cap) - tlo;               // d < 0 (or -0): miss
+            miss = __funnelshift_l(__float_as_uint(d), miss, 1);
         }
     }
-    return hitmask;
+    return ~miss & (imask | lmask);
 }
 
 // Triangle part of hitScene over the wide BVH.  `closest`/`h` carry in the sphere/quad result.
 // Returns true if a triangle was accepted; sets `ambiguous` when the result must be re-derived
-// with the reference-order walk.
-__device__ __forceinline__ bool hit_bvh_wide(const DeviceScene& S, const WideBvh& WB, const Ray& ray, Counts* cnt,
-                                             ObjRayCache& oc, float& closest, HitLite& h, bool& ambiguous) {
+// with the reference-order walk.  `lut` = the block's octant permutation table (wide_lut_init).
+__device__ __forceinline__ bool hit_bvh_wide(const DeviceScene& S, const WideBvh& WB, const unsigned char* lut, const Ray& ray,
+                                             Counts* cnt, ObjRayCache& oc, float& closest, HitLite& h, bool& ambiguous) {
     ambiguous = false;
     if (WB.n_nodes == 0) return false;
     const WideRay wr = make_wide_ray(ray);
+    const unsigned char* lut_r = lut + (wr.octinv << 8);
     bool hit_anything = false;
     uint2 stack[WIDE_STACK];
     int sp = 0;
@@ -105,15 +133,16 @@ __device__ __forceinline__ bool hit_bvh_wide(const DeviceScene& S, const WideBvh
             const uint32_t slot = (bit - 24u) ^ wr.octinv;
             const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << slot) & 0xffu);
             const uint32_t ni = G.x + rel;
-            uint32_t child_base, tri_base, imask;
+            uint32_t child_base, tri_base, imask, lmask;
             n_nodes++;
-            const uint32_t hm = wide_node_hits(WB.nodes, ni, ray, wr, closest, child_base, tri_base, imask);
-            G = make_uint2(child_base, (hm & 0xff000000u) | imask);
-            uint32_t tm = hm & 0x00ffffffu;
+            const uint32_t hits = wide_node_hits(WB.nodes, ni, ray, wr, closest, child_base, tri_base, imask, lmask);
+            G = make_uint2(child_base, ((uint32_t)lut_r[hits & imask] << 24) | imask);
+            uint32_t tm = hits & lmask;
             while (tm) {
                 const int b = __ffs((int)tm) - 1;
                 tm &= tm - 1u;
-                const float4* t = &WB.tris[3 * (size_t)(tri_base + (uint32_t)b)];
+                const uint32_t ti = tri_base + (uint32_t)__popc(lmask & ~(0xffffffffu << b));
+                const float4* t = &WB.tris[3 * (size_t)ti];
                 const float4 A = __ldg(&t[0]), B = __ldg(&t[1]), C = __ldg(&t[2]);
                 oc.fetch(S, __float_as_int(B.w), ray);
                 float dst, uu, vv;
@@ -135,7 +164,7 @@ __device__ __forceinline__ bool hit_bvh_wide(const DeviceScene& S, const WideBvh
 }
 
 // hitScene for the fast path: analytic primitives, wide BVH, reference-order fallback.
-__device__ __forceinline__ bool hitScene_wide(const DeviceScene& S, const WideBvh& WB, const Ray& ray, uint32_t& rng,
+__device__ __forceinline__ bool hitScene_wide(const DeviceScene& S, const WideBvh& WB, const unsigned char* lut, const Ray& ray, uint32_t& rng,
                                               Counts* cnt, ObjRayCache& oc, HitLite& h, unsigned* fallbacks) {
     float closest = WGPT_MAX_FLOAT;
     if (cnt) cnt->rays++;
@@ -143,7 +172,7 @@ __device__ __forceinline__ bool hitScene_wide(const DeviceScene& S, const WideBv
     bool hit = hit_analytic(S, ray, rng, cnt, closest, h);
     const HitLite h0 = h; const float c0 = closest;
     bool ambiguous;
-    bool hit_t = hit_bvh_wide(S, WB, ray, cnt, oc, closest, h, ambiguous);
+    bool hit_t = hit_bvh_wide(S, WB, lut, ray, cnt, oc, closest, h, ambiguous);
     if (ambiguous) {
         h = h0; closest = c0;
         hit_t = hit_bvh_binary(S, ray, nullptr, oc, closest, h);

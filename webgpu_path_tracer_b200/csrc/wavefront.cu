@@ -77,8 +77,13 @@ __device__ __forceinline__ bool root_box_hit(const DeviceScene& S, const Ray& ra
 #define WF_TRI_BATCH 8
 #endif
 
+#ifndef WF_EXTEND_MINB
+#define WF_EXTEND_MINB 7
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, WfParams P) {
+__global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S, WideBvh WB, WfParams P) {
+    __shared__ unsigned char s_lut[WIDE_LUT_BYTES];
+    wide_lut_init(s_lut);
     WfControl* ctl = P.ctl;
     const uint32_t n = ctl->n_extend;
     const uint32_t lane = threadIdx.x & 31u;
@@ -95,7 +100,8 @@ __global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, Wf
     float closest = WGPT_MAX_FLOAT, c0 = WGPT_MAX_FLOAT;
     bool hit_t = false, ambiguous = false;
     uint2 G = make_uint2(0u, 0u);
-    uint32_t tm = 0, tri_base = 0;               // parked candidate triangles of the last node visited
+    uint32_t tm = 0, tri_base = 0, tri_lmask = 0;   // parked candidate triangles of the last node visited: hit leaf slots, first
+                                                    // packed triangle, leaf-slot mask (triangle of slot b = tri_base + popc(lmask below b))
     uint2 stack[WIDE_STACK];
     int sp = 0;
 
@@ -149,11 +155,11 @@ __global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, Wf
                 else {
                     const uint32_t sl = (bit - 24u) ^ wr.octinv;
                     const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << sl) & 0xffu);
-                    uint32_t child_base, imask;
+                    uint32_t child_base, imask, lmask;
                     if (COUNT) c.nodes++;
-                    const uint32_t hm = wide_node_hits(WB.nodes, G.x + rel, ray, wr, closest, child_base, tri_base, imask);
-                    G = make_uint2(child_base, (hm & 0xff000000u) | imask);
-                    tm = hm & 0x00ffffffu;
+                    const uint32_t hits = wide_node_hits(WB.nodes, G.x + rel, ray, wr, closest, child_base, tri_base, imask, lmask);
+                    G = make_uint2(child_base, ((uint32_t)s_lut[(wr.octinv << 8) | (hits & imask)] << 24) | imask);
+                    tm = hits & lmask; tri_lmask = lmask;
                 }
             }
             // ---- triangle phase: one parked triangle per lane, once enough lanes have one ----
@@ -163,7 +169,7 @@ __global__ void __launch_bounds__(128) k_wf_extend(DeviceScene S, WideBvh WB, Wf
                 if (has && tm != 0u) {
                     const int b = __ffs((int)tm) - 1;
                     tm &= tm - 1u;
-                    const float4* t = &WB.tris[3 * (size_t)(tri_base + (uint32_t)b)];
+                    const float4* t = &WB.tris[3 * (size_t)(tri_base + (uint32_t)__popc(tri_lmask & ~(0xffffffffu << b)))];
                     const float4 A = __ldg(&t[0]), B = __ldg(&t[1]), C = __ldg(&t[2]);
                     oc.fetch(S, __float_as_int(B.w), ray);
                     float dst, uu, vv;
@@ -495,6 +501,8 @@ __global__ void __launch_bounds__(128) k_trace_rays_wide(DeviceScene S, WideBvh 
                                                          const uint32_t* __restrict__ seeds, int* __restrict__ out_type,
                                                          int* __restrict__ out_index, float* __restrict__ out_t,
                                                          uint32_t* __restrict__ fallbacks_out) {
+    __shared__ unsigned char s_lut[WIDE_LUT_BYTES];
+    wide_lut_init(s_lut);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     Counts c = {0, 0, 0, 0, 0, 0, 0, 0};
     unsigned fallbacks = 0;
@@ -502,7 +510,7 @@ __global__ void __launch_bounds__(128) k_trace_rays_wide(DeviceScene S, WideBvh 
         Ray r; r.o = V3(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]); r.d = V3(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
         uint32_t rng = seeds ? seeds[i] : 0u;
         ObjRayCache oc; HitLite h; h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.mat_id = -1; h.uu = h.vv = 0.0f;
-        const bool hit = hitScene_wide(S, WB, r, rng, COUNT ? &c : nullptr, oc, h, &fallbacks);
+        const bool hit = hitScene_wide(S, WB, s_lut, r, rng, COUNT ? &c : nullptr, oc, h, &fallbacks);
         out_type[i] = hit ? (h.kind == HIT_VOLUME ? 0 : h.kind) : -1;
         out_index[i] = hit ? (h.kind == HIT_TRI ? (int)S.triangles[h.index].local_id : h.index) : -1;
         out_t[i] = hit ? h.t : 0.0f;

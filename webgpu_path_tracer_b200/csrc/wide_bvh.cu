@@ -9,7 +9,7 @@
 
 namespace wg {
 
-#define WIDE_LEAF_MAX 3
+#define WIDE_LEAF_MAX 1      // a leaf slot holds exactly one triangle (= one leaf of the binary tree)
 
 struct BuildCtx {
     const BvhNode* bvh; int n_bvh;
@@ -106,6 +106,7 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
             if (ext > 0.0) { int k; frexp(ext, &k); e = k - 8; }       // ext in [2^(k-1), 2^k)
             if (e < -126) e = -126;
             while (e < 127 && ldexp(255.0, e) < ext) e++;
+            if (e > 100) B.counters[5] = 1;                 // the traversal folds 2^24 into the scale (trace_wide.cuh cvt2)
             ebits[a] = (uint32_t)(e + 127);
             scale[a] = __uint_as_float(ebits[a] << 23);
         }
@@ -128,10 +129,9 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
         uint32_t q_base = 0;
         if (n_inner) q_base = atomicAdd(&B.counters[3 - parity], n_inner);
 
-        unsigned char meta[8], qlo[3][8], qhi[3][8];
-        uint32_t inner_i = 0, tri_off = 0;
+        unsigned char qlo[3][8], qhi[3][8];
+        uint32_t inner_i = 0, tri_off = 0, lmask = 0;
         for (int s = 0; s < 8; s++) {
-            meta[s] = 0;
             for (int a = 0; a < 3; a++) { qlo[a][s] = 255; qhi[a][s] = 0; }     // empty: inverted box, never hit
             const int c = child_in_slot[s];
             if (c < 0) continue;
@@ -144,25 +144,18 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
                 qlo[a][s] = (unsigned char)l; qhi[a][s] = (unsigned char)h;
             }
             if (imask & (1u << s)) {
-                meta[s] = (unsigned char)(0x20 | (24 + s));
                 B.queue[1 - parity][q_base + inner_i] = make_uint2((uint32_t)c, child_base + inner_i);
                 inner_i++;
             } else {
-                // leaf child: copy its <= 3 triangles (leaves of the binary subtree, in pre-order)
-                const int end = sub_end(B, c);
-                uint32_t cnt = 0;
-                for (int j = c; j < end; j++) {
-                    if (!is_leaf(B, j)) continue;
-                    const int src = (int)B.bvh[j].prim_id;
-                    const Triangle& t = B.tris[src];
-                    float4* o = &B.out_tris[3 * (size_t)(tri_base + tri_off + cnt)];
-                    o[0] = make_float4(t.A[0], t.A[1], t.A[2], __int_as_float(src));
-                    o[1] = make_float4(t.B[0], t.B[1], t.B[2], __int_as_float((int)t.mesh_id));
-                    o[2] = make_float4(t.C[0], t.C[1], t.C[2], __int_as_float((int)t.local_id));
-                    cnt++;
-                }
-                meta[s] = (unsigned char)((((1u << cnt) - 1u) << 5) | tri_off);
-                tri_off += cnt;
+                // leaf slot: the triangle of this binary leaf; the slot's triangles are packed in slot order
+                const int src = (int)B.bvh[c].prim_id;
+                const Triangle& t = B.tris[src];
+                float4* o = &B.out_tris[3 * (size_t)(tri_base + tri_off)];
+                o[0] = make_float4(t.A[0], t.A[1], t.A[2], __int_as_float(src));
+                o[1] = make_float4(t.B[0], t.B[1], t.B[2], __int_as_float((int)t.mesh_id));
+                o[2] = make_float4(t.C[0], t.C[1], t.C[2], __int_as_float((int)t.local_id));
+                lmask |= 1u << s;
+                tri_off++;
             }
         }
 
@@ -170,7 +163,7 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
         uint4* o = &B.out_nodes[5 * (size_t)wide_idx];
         o[0] = make_uint4(__float_as_uint(lo[0]), __float_as_uint(lo[1]), __float_as_uint(lo[2]),
                           ebits[0] | (ebits[1] << 8) | (ebits[2] << 16) | (imask << 24));
-        o[1] = make_uint4(child_base, tri_base, pack4(meta), pack4(meta + 4));
+        o[1] = make_uint4(child_base, tri_base, lmask, 0u);
         o[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
         o[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
         o[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));

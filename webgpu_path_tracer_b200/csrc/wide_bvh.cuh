@@ -7,14 +7,16 @@
 //       child box lo = origin + qlo * 2^(e-127), hi = origin + qhi * 2^(e-127)  (conservative)
 //       imask bit s = slot s holds an inner child
 //   q1: child_base (u32: wide index of the first inner child; inner children are contiguous in
-//       slot order), tri_base (u32: first packed triangle of this node's leaf children, contiguous
-//       in slot order), meta[0..3], meta[4..7]
-//       meta[s]: 0 empty | inner: 0x20 | (24 + s) | leaf: (unary triangle count << 5) | offset
-//       from tri_base (<= 3 triangles per leaf child, <= 24 per node)
+//       slot order), tri_base (u32: first packed triangle of this node's leaf slots, contiguous
+//       in slot order), lmask (u8: bit s = slot s holds ONE triangle), spare
+//       A slot is empty, inner, or exactly one triangle (a leaf of the reference's binary tree
+//       has one triangle, bvhNode.js:28-73), so the triangle of leaf slot s is
+//       tri_base + popc(lmask & ((1 << s) - 1)) and the per-slot work at traversal time is just
+//       the slab test (no per-slot meta byte to decode).  Empty slots carry an inverted box.
 //   q2: qlo_x[8], qlo_y[8]   q3: qlo_z[8], qhi_x[8]   q4: qhi_y[8], qhi_z[8]
 // Slots are assigned so that slot s lies towards the diagonal (s&4 ? +x : -x, s&2 ? +y : -y,
 // s&1 ? +z : -z) from the node centre; a ray with positive-direction code r visits slot s at
-// priority (s ^ r), which needs no sort at traversal time.
+// priority (s ^ r): the hit byte is permuted into that order by one table lookup.
 //
 // PackedTri, 48 bytes = 3 x float4: (A.xyz, src), (B.xyz, mesh), (C.xyz, local_id); src = position
 // in binding 5 (for the normals), mesh = i32(Triangle.mesh_id), local_id = i32(Triangle.local_id),
