@@ -166,6 +166,16 @@ WGPT_HD double exp_d(double t) {
 /* ---- the float entry points the shader restatements call ---- */
 WGPT_HD float sinf_(float x)  { return (float)sin_d((double)x); }
 WGPT_HD float cosf_(float x)  { return (float)cos_d((double)x); }
+/* sinf_(x) and cosf_(x) at once: one reduction, both kernels evaluated by every caller (no
+ * quadrant-dependent control flow, which would split a GPU warp four ways); every lane performs
+ * the same operations as sin_d / cos_d on the same inputs, so the bits equal the separate calls. */
+WGPT_HD void sincosf_(float x, float* s, float* c) {
+    int q; const double r = reduce_pio2((double)x, &q);
+    const double ks = ksin(r), kc = kcos(r);
+    const double sv = (q & 1) ? kc : ks, cv = (q & 1) ? ks : kc;
+    *s = (float)((q & 2) ? -sv : sv);
+    *c = (float)(((q + 1) & 2) ? -cv : cv);
+}
 WGPT_HD float acosf_(float x) { return (float)acos_d((double)x); }
 WGPT_HD float logf_(float x)  { return (float)log_d((double)x); }
 /* WGSL pow(x,y): defined for x >= 0 here; x < 0 -> NaN (the WGSL spec leaves it undefined). */

@@ -132,6 +132,7 @@ static int ensure_pool(wgpt_ctx* c) {
     P.stage = (float4*)carve((size_t)ring * npix * 16);
     P.ring = ring;
     P.items_per_frame = c->shard_pixels;
+    P.inv_items_per_frame = 1.0 / (double)(c->shard_pixels ? c->shard_pixels : 1u);
     if ((size_t)(p - (char*)F->pool_mem) > bytes) return set_err(c, WGPT_E_NOMEM, "pool carve overflow");
     F->capacity = cap; F->ring = ring;
     if ((e = cudaMallocHost((void**)&F->h_flag, 64)) != cudaSuccess) return cuda_err(c, e, "pinned flag");

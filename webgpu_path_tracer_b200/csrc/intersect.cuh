@@ -37,11 +37,12 @@ struct Counts { unsigned rays, nodes, tris, spheres, quads, rng, samples, aborts
 __device__ __forceinline__ v3 ld3(const float* p) { return V3(p[0], p[1], p[2]); }
 __device__ __forceinline__ v3 at(const Ray& r, float t) { return r.o + t * r.d; }
 
-// common.wgsl:7-12; the divisor 4294967295 rounds to 2^32 in f32
+// common.wgsl:7-12; the divisor 4294967295 rounds to 2^32 in f32, and dividing by a power of two
+// is the same correctly rounded value as multiplying by its (exact) reciprocal
 __device__ __forceinline__ float rand2D(uint32_t& s) {
     s = s * 747796405u + 2891336453u;
     const uint32_t word = ((s >> ((s >> 28u) + 4u)) ^ s) * 277803737u;
-    return fd((float)((word >> 22u) ^ word), 4294967296.0f);
+    return fm((float)((word >> 22u) ^ word), 2.3283064365386962890625e-10f);
 }
 
 // roots of common.wgsl:33-52 / :78-97; returns false when no root lies in (tmin, tmax)

@@ -57,10 +57,12 @@ __device__ __forceinline__ float reflectance(float cosine, float ref_idx) {
 __device__ __forceinline__ v3 uniform_random_in_unit_sphere(uint32_t& rng) {
     const float phi = fm(fm(rand2D(rng), 2.0f), WGPT_PI_F);
     const float theta = wgpt_pm::acosf_(fs(fm(2.0f, rand2D(rng)), 1.0f));
-    const float st = wgpt_pm::sinf_(theta);
-    const float x = fm(st, wgpt_pm::cosf_(phi));
-    const float y = fm(st, wgpt_pm::sinf_(phi));
-    const float z = wgpt_pm::cosf_(theta);
+    float st, ct, sp, cp;
+    wgpt_pm::sincosf_(theta, &st, &ct);
+    wgpt_pm::sincosf_(phi, &sp, &cp);
+    const float x = fm(st, cp);
+    const float y = fm(st, sp);
+    const float z = ct;
     return normalize(V3(x, y, z));
 }
 
@@ -70,7 +72,9 @@ __device__ __forceinline__ v3 cosine_sampling_wrt_Z(uint32_t& rng) {
     const float r2 = rand2D(rng);
     const float phi = fm(WGPT_TWO_PI_F, r1);
     const float sr2 = fsq(r2);
-    return V3(fm(wgpt_pm::cosf_(phi), sr2), fm(wgpt_pm::sinf_(phi), sr2), fsq(fs(1.0f, r2)));
+    float sp, cp;
+    wgpt_pm::sincosf_(phi, &sp, &cp);
+    return V3(fm(cp, sr2), fm(sp, sr2), fsq(fs(1.0f, r2)));
 }
 
 // importanceSampling.wgsl:60-71
@@ -147,7 +151,9 @@ __device__ __forceinline__ Ray material_scatter(const Material& m, const Ray& ra
         const float sin_hg = fsq(fs(1.0f, fm(cos_hg, cos_hg)));
         const float phi = fm(WGPT_TWO_PI_F, rand2D(rng));
         draws += 2;
-        const v3 hg_dir = V3(fm(sin_hg, wgpt_pm::cosf_(phi)), fm(sin_hg, wgpt_pm::sinf_(phi)), cos_hg);
+        float sp, cp;
+        wgpt_pm::sincosf_(phi, &sp, &cp);
+        const v3 hg_dir = V3(fm(sin_hg, cp), fm(sin_hg, sp), cos_hg);
         onb_build_from_w(st, ray_in.d);
         scattered.o = st.p;
         scattered.d = normalize(onb_get_local(st, hg_dir));

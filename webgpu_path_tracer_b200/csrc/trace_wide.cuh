@@ -22,13 +22,16 @@ struct WideRay {
     uint32_t octinv;          // bit 2/1/0 set when d.x/y/z >= 0
 };
 
+__device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
 __device__ __forceinline__ WideRay make_wide_ray(const Ray& r) {
     WideRay w;
     const float eps = 1e-12f;
     const float dx = fabsf(r.d.x) < eps ? copysignf(eps, r.d.x) : r.d.x;
     const float dy = fabsf(r.d.y) < eps ? copysignf(eps, r.d.y) : r.d.y;
     const float dz = fabsf(r.d.z) < eps ? copysignf(eps, r.d.z) : r.d.z;
-    w.idx = 1.0f / dx; w.idy = 1.0f / dy; w.idz = 1.0f / dz;
+    // box tests only (conservative, 2^-19 slack): the 1-ulp MUFU.RCP is enough, |d| is in [1e-12, ~1]
+    w.idx = rcp_approx(dx); w.idy = rcp_approx(dy); w.idz = rcp_approx(dz);
     w.octinv = (r.d.x >= 0.0f ? 4u : 0u) | (r.d.y >= 0.0f ? 2u : 0u) | (r.d.z >= 0.0f ? 1u : 0u);
     return w;
 }

@@ -249,7 +249,7 @@ __device__ __forceinline__ void start_sample(const DeviceScene& S, uint32_t pixe
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
     __shared__ uint32_t s_done[WF_MAX_RING];
-    __shared__ uint32_t s_cnt[8][WF_CLASSES + 1];      // per warp, per class
+    __shared__ uint32_t s_key_cnt[32];                 // slots per shade key
     __shared__ int4 s_hid[256];
     __shared__ uint32_t s_perm[256];
     __shared__ uint32_t s_warp[8];
@@ -258,28 +258,32 @@ __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     if (threadIdx.x < WF_MAX_RING) s_done[threadIdx.x] = 0;
 
-    // ---- material sort inside the block: slot (block base + j) -> thread rank by (class, j) ----
+    // ---- material sort inside the block: slot (block base + j) -> thread rank by shade key ----
+    // key = (material class, hit kind) for hits, then miss / idle / dead / trace: warps end up
+    // shading one material AND one primitive type (finalize_hit differs per kind).  Counting sort
+    // with warp-aggregated shared atomics; the order inside a key does not matter.
     const uint32_t block_base = blockIdx.x * blockDim.x;
+    if (threadIdx.x < 32) s_key_cnt[threadIdx.x] = 0;
     {
         const uint32_t s0 = block_base + threadIdx.x;
         int4 hid = make_int4(HIT_NONE, -1, -1, WF_CLS_DEAD);
         if (s0 < P.pool.capacity) hid = P.pool.hid[s0];
         s_hid[threadIdx.x] = hid;
-        const int cls = hid.w;
-        uint32_t my_rank_in_warp = 0;
-        #pragma unroll
-        for (int k = 0; k < WF_CLASSES; k++) {
-            const uint32_t m = __ballot_sync(0xffffffffu, cls == k);
-            if (cls == k) my_rank_in_warp = (uint32_t)__popc(m & lanemask_lt());
-            if (lane == 0) s_cnt[warp][k] = (uint32_t)__popc(m);
-        }
+        const uint32_t key = hid.w < WF_CLS_MISS ? (uint32_t)(hid.w * 4 + (hid.x & 3)) : (uint32_t)(12 + hid.w);
+        const uint32_t peers = __match_any_sync(0xffffffffu, key);
+        const int leader = __ffs((int)peers) - 1;
         __syncthreads();
-        // exclusive offset of (class, warp) in class-major order
-        uint32_t off = 0;
-        for (int k = 0; k < cls; k++)
-            for (int w = 0; w < 8; w++) off += s_cnt[w][k];
-        for (uint32_t w = 0; w < warp; w++) off += s_cnt[w][cls];
-        s_perm[off + my_rank_in_warp] = threadIdx.x;
+        uint32_t warp_base = 0;
+        if ((int)lane == leader) warp_base = atomicAdd(&s_key_cnt[key], (uint32_t)__popc(peers));
+        warp_base = __shfl_sync(0xffffffffu, warp_base, leader);
+        __syncthreads();
+        // exclusive scan over the 32 key counters, redundantly per warp (no extra barrier)
+        const uint32_t mine = s_key_cnt[lane];
+        uint32_t incl = mine;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if ((int)lane >= o) incl += t; }
+        const uint32_t key_off = __shfl_sync(0xffffffffu, incl - mine, (int)key);
+        s_perm[key_off + warp_base + (uint32_t)__popc(peers & lanemask_lt())] = threadIdx.x;
         __syncthreads();
     }
     const uint32_t j = s_perm[threadIdx.x];
@@ -369,9 +373,14 @@ __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
                 const uint32_t r = (uint32_t)__popc(m & lanemask_lt());
                 new_cls = more_later ? WF_CLS_IDLE : WF_CLS_DEAD;
                 if (r < granted) {
-                    const unsigned long long w = old + r;
-                    frame_k = (uint32_t)(w / P.items_per_frame);
-                    pix_i = (uint32_t)(w - (unsigned long long)frame_k * P.items_per_frame);
+                    // (frame ordinal, pixel) of item `old + r` without a 64-bit division: quotient
+                    // estimate in binary64 (exact to +-1 for old < 2^52), fixed up with integers
+                    uint32_t fk0 = (uint32_t)__double2ull_rz(__ull2double_rz(old) * P.inv_items_per_frame);
+                    long long rem = (long long)(old - (unsigned long long)fk0 * P.items_per_frame) + (long long)r;
+                    if (rem < 0) { fk0--; rem += P.items_per_frame; }
+                    while (rem >= (long long)P.items_per_frame) { fk0++; rem -= P.items_per_frame; }
+                    frame_k = fk0;
+                    pix_i = (uint32_t)rem;
                     const uint32_t pixel = shard_pixel(S.shard, S.W, pix_i);
                     const uint32_t lim_pix = npix < S.shard.pixel_limit ? npix : S.shard.pixel_limit;
                     if (pixel < lim_pix) {

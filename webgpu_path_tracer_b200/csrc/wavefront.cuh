@@ -56,6 +56,7 @@ struct WfParams {
     float4* stage;                     // ring x W*H: (pixColor, 1)
     uint32_t ring;                     // frames in flight
     uint32_t items_per_frame;          // shard.n_pixels
+    double inv_items_per_frame;        // 1.0 / items_per_frame (quotient estimate, fixed up with integers)
     int frame0, frame_stride;          // frame number of ordinal k = frame0 + k * frame_stride
     // optional probe outputs (first closest-hit query of every pixel), indexed by pixel
     int* prim_type; int* prim_index; float* prim_t;
