@@ -108,9 +108,9 @@ static int ensure_pool(wgpt_ctx* c) {
     if (F->pool_ready) return WGPT_OK;
     const uint32_t npix = (uint32_t)c->cfg.width * c->cfg.height;
     uint32_t cap = (uint32_t)env_int("WGPT_POOL", 0);
-    if (!cap) cap = std::min<uint64_t>(1u << 21, (uint64_t)c->shard_pixels * 4);
+    if (!cap) cap = std::min<uint64_t>(1u << 23, (uint64_t)c->shard_pixels * 4);
     cap = std::max(1024u, (cap + 1023u) & ~1023u);
-    uint32_t ring = (uint32_t)env_int("WGPT_RING", 32);
+    uint32_t ring = (uint32_t)env_int("WGPT_RING", 64);
     ring = std::max(2u, std::min<uint32_t>(ring, WF_MAX_RING));
     // one allocation, carved into 16-byte-aligned arrays
     const size_t per_slot = 8 * 16 + 4;

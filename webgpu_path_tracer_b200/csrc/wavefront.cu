@@ -83,9 +83,10 @@ __device__ __forceinline__ bool root_box_hit(const DeviceScene& S, const Ray& ra
 template <bool COUNT>
 __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S, WideBvh WB, WfParams P) {
     __shared__ unsigned char s_lut[WIDE_LUT_BYTES];
-    wide_lut_init(s_lut);
     WfControl* ctl = P.ctl;
     const uint32_t n = ctl->n_extend;
+    if (n == 0) return;                                    // nothing queued (e.g. the iterations after the last frame finished)
+    wide_lut_init(s_lut);
     const uint32_t lane = threadIdx.x & 31u;
     Counts c = {0, 0, 0, 0, 0, 0, 0, 0};
     unsigned fallbacks = 0;
@@ -246,15 +247,22 @@ __device__ __forceinline__ void start_sample(const DeviceScene& S, uint32_t pixe
     ray = sample_ray(S, ps, si, sj, rng);
 }
 
+#ifndef WF_SHADE_THREADS
+#define WF_SHADE_THREADS 256
+#endif
+#ifndef WF_SHADE_MINB
+#define WF_SHADE_MINB 4
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
+__global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(DeviceScene S, WfParams P) {
     __shared__ uint32_t s_done[WF_MAX_RING];
     __shared__ uint32_t s_key_cnt[32];                 // slots per shade key
-    __shared__ int4 s_hid[256];
-    __shared__ uint32_t s_perm[256];
-    __shared__ uint32_t s_warp[8];
+    __shared__ int4 s_hid[WF_SHADE_THREADS];
+    __shared__ uint32_t s_perm[WF_SHADE_THREADS];
+    __shared__ uint32_t s_warp[WF_SHADE_THREADS / 32];
     __shared__ uint32_t s_base;
     WfControl* ctl = P.ctl;
+    if (ctl->finished) return;                             // the host notices the flag one batch late: those launches are empty
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     if (threadIdx.x < WF_MAX_RING) s_done[threadIdx.x] = 0;
 
@@ -431,7 +439,7 @@ __global__ void __launch_bounds__(256) k_wf_shade(DeviceScene S, WfParams P) {
     __syncthreads();
     if (threadIdx.x == 0) {
         uint32_t sum = 0;
-        for (int k = 0; k < 8; k++) { const uint32_t v = s_warp[k]; s_warp[k] = sum; sum += v; }
+        for (int k = 0; k < WF_SHADE_THREADS / 32; k++) { const uint32_t v = s_warp[k]; s_warp[k] = sum; sum += v; }
         s_base = sum ? atomicAdd(&ctl->n_next, sum) : 0u;
     }
     __syncthreads();
@@ -492,9 +500,9 @@ void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams
     if (S.counters) k_wf_extend<true><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     if (ev) cudaEventRecord(ev[1], stream);
-    const unsigned shade_blocks = (P.pool.capacity + 255u) / 256u;
-    if (S.counters) k_wf_shade<true><<<shade_blocks, 256, 0, stream>>>(S, P);
-    else k_wf_shade<false><<<shade_blocks, 256, 0, stream>>>(S, P);
+    const unsigned shade_blocks = (P.pool.capacity + WF_SHADE_THREADS - 1u) / WF_SHADE_THREADS;
+    if (S.counters) k_wf_shade<true><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P);
+    else k_wf_shade<false><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P);
     if (ev) cudaEventRecord(ev[2], stream);
     k_wf_ctl_end<<<1, 32, 0, stream>>>(P);
     const uint32_t npix = (uint32_t)S.W * (uint32_t)S.H;
