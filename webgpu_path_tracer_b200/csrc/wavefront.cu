@@ -259,12 +259,13 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     __shared__ uint32_t s_key_cnt[32];                 // slots per shade key
     __shared__ int4 s_hid[WF_SHADE_THREADS];
     __shared__ uint32_t s_perm[WF_SHADE_THREADS];
-    __shared__ uint32_t s_warp[WF_SHADE_THREADS / 32];
-    __shared__ uint32_t s_base;
+    __shared__ uint32_t s_q[WF_SHADE_THREADS];          // slot ids for the next ray queue
+    __shared__ uint32_t s_qn, s_arrived;
     WfControl* ctl = P.ctl;
     if (ctl->finished) return;                             // the host notices the flag one batch late: those launches are empty
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     if (threadIdx.x < WF_MAX_RING) s_done[threadIdx.x] = 0;
+    if (threadIdx.x == 0) { s_qn = 0; s_arrived = 0; }
 
     // ---- material sort inside the block: slot (block base + j) -> thread rank by shade key ----
     // key = (material class, hit kind) for hits, then miss / idle / dead / trace: warps end up
@@ -303,8 +304,8 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     const int side = S.K.STRATIFY ? strat_side(S) : 1;
     const uint32_t samples_per_item = S.K.STRATIFY ? (uint32_t)(side * side) : (uint32_t)S.K.NUM_SAMPLES;
 
-    bool alive = false, need_work = false, store_pix = false;
-    uint32_t rng = 0, pix_i = 0, frame_k = 0, bounce = 0, scnt = 0;
+    bool alive = false, need_work = false, store_pix = false, gen = false;
+    uint32_t rng = 0, pix_i = 0, frame_k = 0, bounce = 0, scnt = 0, gen_pixel = 0;
     unsigned n_samples = 0, n_draws = 0;
     Counts cnt = {0, 0, 0, 0, 0, 0, 0, 0};
     Ray ray; ray.o = ray.d = V3s(0.0f);
@@ -346,10 +347,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
             scnt++;
             const uint32_t pixel = shard_pixel(S.shard, S.W, pix_i);
             if (scnt < samples_per_item) {
-                start_sample(S, pixel, scnt, side, rng, ray);              // next sample, same RNG stream
-                n_draws += 2; n_samples++;
-                thr = V3s(1.0f); acc = V3s(0.0f); bounce = 0;
-                alive = true; store_pix = true;
+                gen = true; gen_pixel = pixel;                             // next sample, same RNG stream
             } else {
                 const float div = S.K.STRATIFY ? pix.w : (float)S.K.NUM_SAMPLES;
                 P.stage[(size_t)(frame_k % P.ring) * npix + pixel] = make_float4(fd(pix.x, div), fd(pix.y, div), fd(pix.z, div), 1.0f);
@@ -394,12 +392,9 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
                     if (pixel < lim_pix) {
                         const float frame = (float)(P.frame0 + (int)frame_k * P.frame_stride);
                         rng = pixel_seed(pixel, frame);
-                        scnt = 0; bounce = 0;
-                        start_sample(S, pixel, 0, side, rng, ray);
-                        n_draws += 2; n_samples++;
-                        thr = V3s(1.0f); acc = V3s(0.0f);
+                        scnt = 0;
                         pix = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-                        alive = true; store_pix = true;
+                        gen = true; gen_pixel = pixel;
                     } else {
                         atomicAdd(&s_done[frame_k % P.ring], 1u);      // tile tail past the image: nothing to render
                         new_cls = WF_CLS_IDLE;                         // try again next iteration
@@ -407,6 +402,14 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
                 }
             }
         }
+    }
+
+    // ---- camera ray of a new sample: next sample of the same item, or first sample of a new item ----
+    if (gen) {
+        start_sample(S, gen_pixel, scnt, side, rng, ray);
+        n_draws += 2; n_samples++;
+        thr = V3s(1.0f); acc = V3s(0.0f); bounce = 0;
+        alive = true; store_pix = true;
     }
 
     // ---- the new ray's sphere/quad part of hitScene (hitRay.wgsl:6-40) runs here, where all lanes are
@@ -433,18 +436,35 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         P.pool.hid[slot].w = new_cls;               // idle (waiting for the window) or dead (no work left)
     }
 
-    // ---- compact: rays that need the BVH into the next ray queue, one atomic per block ----
-    const uint32_t m = __ballot_sync(0xffffffffu, trace);
-    if (lane == 0) s_warp[warp] = (uint32_t)__popc(m);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t sum = 0;
-        for (int k = 0; k < WF_SHADE_THREADS / 32; k++) { const uint32_t v = s_warp[k]; s_warp[k] = sum; sum += v; }
-        s_base = sum ? atomicAdd(&ctl->n_next, sum) : 0u;
+    // ---- compact: rays that need the BVH into the next ray queue, one global atomic per block ----
+    // No block barrier here: warps finish at very different times (a miss warp is done long before
+    // a glossy one), so every warp parks its slot ids in shared memory and leaves; the LAST warp
+    // to arrive publishes the block's entries and its finished-item counts.
+    {
+        const uint32_t m = __ballot_sync(0xffffffffu, trace);
+        if (m) {
+            uint32_t wbase = 0;
+            if (lane == 0) wbase = atomicAdd(&s_qn, (uint32_t)__popc(m));
+            wbase = __shfl_sync(0xffffffffu, wbase, 0);
+            if (trace) s_q[wbase + (uint32_t)__popc(m & lanemask_lt())] = slot;
+        }
+        __syncwarp();
+        uint32_t last = 0;
+        if (lane == 0) { __threadfence_block(); last = atomicAdd(&s_arrived, 1u) == WF_SHADE_THREADS / 32 - 1 ? 1u : 0u; }
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (last) {
+            __threadfence_block();
+            const uint32_t total = *(volatile uint32_t*)&s_qn;
+            uint32_t base = 0;
+            if (lane == 0 && total) base = atomicAdd(&ctl->n_next, total);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            for (uint32_t i = lane; i < total; i += 32) P.q_extend[base + i] = ((volatile uint32_t*)s_q)[i];
+            for (uint32_t k = lane; k < WF_MAX_RING; k += 32) {
+                const uint32_t v = ((volatile uint32_t*)s_done)[k];
+                if (v) atomicAdd(&ctl->done[k], v);
+            }
+        }
     }
-    __syncthreads();
-    if (trace) P.q_extend[s_base + s_warp[warp] + (uint32_t)__popc(m & lanemask_lt())] = slot;
-    if (threadIdx.x < WF_MAX_RING && s_done[threadIdx.x]) atomicAdd(&ctl->done[threadIdx.x], s_done[threadIdx.x]);
 
     if (COUNT) {
         cnt.samples += n_samples; cnt.rng += n_draws;
