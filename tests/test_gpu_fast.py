@@ -112,3 +112,41 @@ def test_wide_traversal_equals_reference_walk_on_random_rays(golden_meshes):
     o.write_scene(scene.buffers())
     tb, ib, db = o.trace_rays(rays[:20000], seeds[:20000], brute_force=False)
     assert np.array_equal(tb, tg[:20000]) and np.array_equal(ib, ig[:20000]) and np.array_equal(bits(db), bits(dg[:20000]))
+
+
+def test_coplanar_ties_resolve_like_the_reference_walk():
+    """The atrium stand-in is full of coplanar, overlapping faces (column caps on the floor and under the
+    lintels): rays hit two triangles at exactly the same distance and the reference keeps the one it visits
+    last.  The fast path must reproduce that through its tie resolver (restricted reference-order walk)."""
+    from webgpu_path_tracer_b200 import meshgen, Scene, Camera
+    m = meshgen.atrium(target_tris=9000)
+    s = Scene(default=False)
+    s.objs.append([])
+    am = s.add_material
+    s.add_quad([-0.5, 0.995, -0.4], [1.0, 0, 0], [0, 0, 0.8], am("light", 0, [0, 0, 0], [0, 0, 0], [20, 20, 20], 0, 0, 0))
+    s.lights.append(s.quads[0])
+    s.objs.append(list(s.quads))
+    s.add_mesh(m, am("stone", 0, [0.76, 0.70, 0.51], [0.76, 0.70, 0.51], [0, 0, 0], 0.05, 0.95, 0))
+    s.create_meshes()
+    s.create_bvh()
+    cam = Camera()
+    cam.set_camera([-1.8, -0.3, 0.0], [1.0, -0.1, 0.1], [0, 1, 0])
+    W, H = 192, 108
+    o = setup(Oracle(W, H), s, cam)
+    g = setup(PathTracer(W, H, mode=MODE_FAST), s, cam)
+    ro, to, io, do = o.probe()
+    rg, tg, ig, dg = g.probe()
+    assert int((to != tg).sum() + (io != ig).sum()) == 0
+    assert np.array_equal(bits(do), bits(dg))
+    o.render(1, 4)
+    g.render(1, 4)
+    assert np.array_equal(bits(o.read_framebuffer()), bits(g.read_framebuffer()))
+    assert g.fast_statistics()["fallback_rays"] > 0          # the resolver really ran
+    # closest-hit hook on random rays inside the atrium, against the exact-mode kernel
+    e = PathTracer(8, 8, mode=MODE_EXACT)
+    e.write_scene(s.buffers())
+    rays, seeds = scenes.random_rays(500_000, 11)
+    te, ie, de = e.trace_rays(rays, seeds)
+    tg, ig, dg = g.trace_rays(rays, seeds)
+    assert int((te != tg).sum()) == 0 and int((ie != ig).sum()) == 0
+    assert np.array_equal(bits(de), bits(dg))

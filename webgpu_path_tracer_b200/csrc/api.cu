@@ -211,8 +211,10 @@ int wgpt_write_buffer(wgpt_ctx* c, int binding, const void* data, size_t bytes) 
     if (binding == 9) {
         const BvhNode* b = (const BvhNode*)data;
         const long long n = (long long)(bytes / 48);
-        c->bvh_prim_end_max = 0; c->bvh_bad = false;
+        c->bvh_prim_end_max = 0; c->bvh_bad = false; c->bvh_depth = 0;
+        std::vector<unsigned short> depth((size_t)n, 0);     // root = 0; the reference's stack never holds more than the leaf depth
         for (long long i = 0; i < n; i++) {
+            if (depth[i] > c->bvh_depth) c->bvh_depth = depth[i];
             if ((int)b[i].prim_type == 2) {
                 const long long s0 = (long long)b[i].prim_id, cnt = (long long)b[i].prim_count;
                 if (s0 < 0 || cnt < 0) { c->bvh_bad = true; break; }
@@ -221,6 +223,7 @@ int wgpt_write_buffer(wgpt_ctx* c, int binding, const void* data, size_t bytes) 
                 const long long r = (long long)b[i].right_offset;
                 const int ax = (int)b[i].axis;
                 if (r <= i || r >= n || i + 1 >= n || ax < 0 || ax > 2) { c->bvh_bad = true; break; }
+                depth[i + 1] = depth[r] = (unsigned short)(depth[i] + 1);
             }
         }
     }

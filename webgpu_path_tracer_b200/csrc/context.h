@@ -33,6 +33,7 @@ struct wgpt_ctx {
     // summary of the big device-only tables, gathered at upload time for validation
     int tri_mesh_max = -1; bool tri_bad = false;
     long long bvh_prim_end_max = 0; bool bvh_bad = false;
+    int bvh_depth = 0;                     // deepest leaf of the binary BVH (root = 0)
     std::string err;
 };
 

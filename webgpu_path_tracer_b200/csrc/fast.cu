@@ -113,7 +113,7 @@ static int ensure_pool(wgpt_ctx* c) {
     uint32_t ring = (uint32_t)env_int("WGPT_RING", 64);
     ring = std::max(2u, std::min<uint32_t>(ring, WF_MAX_RING));
     // one allocation, carved into 16-byte-aligned arrays
-    const size_t per_slot = 8 * 16 + 4;
+    const size_t per_slot = 8 * 16 + 4 + 4;
     const size_t bytes = (size_t)cap * per_slot + (size_t)ring * npix * 16 + 32 * 256;
     cudaError_t e;
     if ((e = cudaMalloc(&F->pool_mem, bytes)) != cudaSuccess) return cuda_err(c, e, "wavefront pool alloc");
@@ -129,6 +129,7 @@ static int ensure_pool(wgpt_ctx* c) {
     P.pool.hid = (int4*)carve((size_t)cap * 16);   P.pool.misc = (uint4*)carve((size_t)cap * 16);
     P.pool.capacity = cap;
     P.q_extend = (uint32_t*)carve((size_t)cap * 4);
+    P.q_fallback = (uint32_t*)carve((size_t)cap * 4);
     P.stage = (float4*)carve((size_t)ring * npix * 16);
     P.ring = ring;
     P.items_per_frame = c->shard_pixels;
@@ -170,6 +171,7 @@ int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_firs
     if (my_frames == 0) return WGPT_OK;
     WfParams P = F->P;
     P.frame0 = f0; P.frame_stride = world;
+    P.bvh_depth = c->bvh_depth;
     P.prim_type = d_ptype; P.prim_index = d_pindex; P.prim_t = d_pt;
     const DeviceScene S = make_device_scene(c, 0xffffffffu);
     const WideBvh WB = wide_view(F);

@@ -32,8 +32,13 @@ __device__ __forceinline__ bool hit_analytic(const DeviceScene& S, const Ray& ra
 }
 
 // BVH part (hitRay.wgsl:42-110).  `closest` carries in the sphere/quad result.
+// `box_tmin` is the lower end of the ray interval for the SLAB tests only (triangles always use
+// the reference's tmin); the reference's value is WGPT_RAY_TMIN.  The tie resolver of the fast path
+// raises it to just below the known closest distance, which skips subtrees that cannot hold a
+// triangle at that distance without changing the visit order of the ones that can.
 __device__ __forceinline__ bool hit_bvh_binary(const DeviceScene& S, const Ray& ray, Counts* cnt,
-                                               ObjRayCache& oc, float& closest, HitLite& h) {
+                                               ObjRayCache& oc, float& closest, HitLite& h,
+                                               float box_tmin = WGPT_RAY_TMIN) {
     if (S.NUM_AABB <= 0) return false;
     bool hit_anything = false;
     const v3 invDir = 1.0f / ray.d;
@@ -47,7 +52,7 @@ __device__ __forceinline__ bool hit_bvh_binary(const DeviceScene& S, const Ray& 
         const float4 a = __ldg(&nodes[3 * cur]);         // min.xyz, right_offset
         const float4 b = __ldg(&nodes[3 * cur + 1]);     // max.xyz, prim_type
         n_nodes++;
-        if (hit_aabb(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), WGPT_RAY_TMIN, closest, ray.o, invDir)) {
+        if (hit_aabb(V3(a.x, a.y, a.z), V3(b.x, b.y, b.z), box_tmin, closest, ray.o, invDir)) {
             if ((int)b.w == 2) {                         // leaf
                 const float4 c = __ldg(&nodes[3 * cur + 2]);   // prim_id, prim_count, skip_link, axis
                 const int start = (int)c.x, count = (int)c.y;

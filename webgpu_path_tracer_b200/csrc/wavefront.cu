@@ -40,7 +40,7 @@ __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
         c->total_work = (unsigned long long)n_frames * P.items_per_frame;
         const unsigned long long win = (unsigned long long)P.ring * P.items_per_frame;
         c->work_limit = win < c->total_work ? win : c->total_work;
-        c->n_extend = 0; c->extend_cursor = 0; c->n_next = 0;
+        c->n_extend = 0; c->extend_cursor = 0; c->n_next = 0; c->n_fallback = 0;
         for (int k = 0; k < WF_MAX_RING; k++) c->done[k] = 0;
         c->acc_k = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
         c->finished = n_frames == 0 ? 1u : 0u; c->fallbacks = 0; c->iterations = 0;
@@ -89,17 +89,16 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
     wide_lut_init(s_lut);
     const uint32_t lane = threadIdx.x & 31u;
     Counts c = {0, 0, 0, 0, 0, 0, 0, 0};
-    unsigned fallbacks = 0;
 
     bool has = false, exhausted = (n == 0);
     uint32_t slot = 0;
     Ray ray; ray.o = ray.d = V3s(0.0f);
     WideRay wr; wr.idx = wr.idy = wr.idz = 0.0f; wr.octinv = 0;
     ObjRayCache oc; oc.reset();
-    HitLite h, h0;
-    h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1; h0 = h;
-    float closest = WGPT_MAX_FLOAT, c0 = WGPT_MAX_FLOAT;
-    bool hit_t = false, ambiguous = false;
+    HitLite h;
+    h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1;
+    float closest = WGPT_MAX_FLOAT;
+    bool hit_t = false, hit_a = false, ambiguous = false, tie = false;
     uint2 G = make_uint2(0u, 0u);
     uint32_t tm = 0, tri_base = 0, tri_lmask = 0;   // parked candidate triangles of the last node visited: hit leaf slots, first
                                                     // packed triangle, leaf-slot mask (triangle of slot b = tri_base + popc(lmask below b))
@@ -124,11 +123,11 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                         const int4 hid = P.pool.hid[slot];
                         ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
                         // sphere/quad result carried in by shade
-                        h0.t = h4.x; h0.uu = 0.0f; h0.vv = 0.0f; h0.kind = hid.x; h0.index = hid.y; h0.mat_id = hid.z;
-                        c0 = hid.x == HIT_NONE ? WGPT_MAX_FLOAT : h4.x;
-                        h = h0; closest = c0;
+                        h.t = h4.x; h.uu = 0.0f; h.vv = 0.0f; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
+                        hit_a = hid.x != HIT_NONE;
+                        closest = hit_a ? h4.x : WGPT_MAX_FLOAT;
                         oc.reset();
-                        hit_t = false; ambiguous = false; sp = 0; tm = 0;
+                        hit_t = false; ambiguous = false; tie = false; sp = 0; tm = 0;
                         wr = make_wide_ray(ray);
                         G = make_uint2(0u, 0x80000000u);
                         has = true;
@@ -176,7 +175,8 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     float dst, uu, vv;
                     if (COUNT) c.tris++;
                     if (tri_test(V3(A.x, A.y, A.z), V3(B.x, B.y, B.z), V3(C.x, C.y, C.z), oc.oray, WGPT_RAY_TMIN, closest, dst, uu, vv)) {
-                        if (hit_t && dst == closest) { ambiguous = true; G.y = 0u; sp = 0; tm = 0u; }   // equal-distance triangles: visit order decides
+                        tie = hit_t && dst == closest;                      // equal-distance triangles: visit order decides (resolved
+                                                                            // by k_wf_fallback); a strictly closer hit clears it
                         hit_t = true; closest = dst;
                         h.t = dst; h.kind = HIT_TRI; h.index = __float_as_int(A.w); h.uu = uu; h.vv = vv;
                         h.mat_id = oc.m.material_id;
@@ -185,18 +185,23 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
             }
             // ---- lanes whose walk is over write their result back and free the lane ----
             if (has && tm == 0u && !(G.y & 0xff000000u) && sp == 0) {
-                if (ambiguous) {                                   // re-derive in reference order
-                    h = h0; closest = c0;
-                    hit_t = hit_bvh_binary(S, ray, nullptr, oc, closest, h);
-                    fallbacks++;
-                }
-                const bool hit = (h0.kind != HIT_NONE) | hit_t;
-                P.pool.hit[slot] = make_float4(h.t, h.uu, h.vv, 0.0f);
-                const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
-                P.pool.hid[slot] = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
-                if (P.prim_type) {
-                    const uint4 misc = P.pool.misc[slot];
-                    if (misc.w == 0u) write_probe(S, P, misc.y, hit, h);     // first query of the item: the primary ray
+                if (ambiguous | tie) {
+                    // equal-distance triangles or a stack overflow: the reference-order walk decides.  The slot
+                    // still holds the ray and its sphere/quad result, so it is only queued here and resolved by
+                    // k_wf_fallback with full warps (inline, one such ray stalled the other 31 lanes).
+                    // A tie (two triangles at exactly the closest distance; the reference keeps the one it visits
+                    // last) carries that distance along, an overflow of the wide stack does not.
+                    if (tie) reinterpret_cast<float*>(&P.pool.hit[slot])[1] = closest;
+                    P.q_fallback[atomicAdd(&ctl->n_fallback, 1u)] = slot | (tie ? 0x80000000u : 0u);
+                } else {
+                    const bool hit = hit_a | hit_t;
+                    P.pool.hit[slot] = make_float4(h.t, h.uu, h.vv, 0.0f);
+                    const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
+                    P.pool.hid[slot] = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
+                    if (P.prim_type) {
+                        const uint4 misc = P.pool.misc[slot];
+                        if (misc.w == 0u) write_probe(S, P, misc.y, hit, h);     // first query of the item: the primary ray
+                    }
                 }
                 has = false;
             }
@@ -215,8 +220,38 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
             if (lane == 0 && x) atomicAdd(&S.counters[k], x);
         }
     }
-    for (int o = 16; o > 0; o >>= 1) fallbacks += __shfl_down_sync(0xffffffffu, fallbacks, o);
-    if (lane == 0 && fallbacks) atomicAdd(&ctl->fallbacks, fallbacks);
+}
+
+// Rays the wide walk could not decide (queued by k_wf_extend), re-traced with the reference-order
+// binary walk (hitRay.wgsl:42-110), one ray per thread.
+__global__ void __launch_bounds__(128) k_wf_fallback(DeviceScene S, WfParams P) {
+    WfControl* ctl = P.ctl;
+    const uint32_t n = ctl->n_fallback;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t entry = P.q_fallback[i];
+        const uint32_t slot = entry & 0x7fffffffu;
+        const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot], h4 = P.pool.hit[slot];
+        const int4 hid = P.pool.hid[slot];
+        Ray ray; ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
+        HitLite h; h.t = h4.x; h.uu = 0.0f; h.vv = 0.0f; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
+        const bool hit_a = hid.x != HIT_NONE;
+        float closest = hit_a ? h4.x : WGPT_MAX_FLOAT;
+        ObjRayCache oc; oc.reset();
+        // Tie with known closest distance D = h4.y: every triangle at distance D lies in nodes whose slab
+        // interval reaches D, and the reference reaches those nodes in the same order whatever else it
+        // visits, so the walk only needs the nodes overlapping [D(1 - 1e-4), closest].  (Not when the
+        // reference's stack guard could fire: its abort depends on everything visited.)
+        const bool restricted = (entry & 0x80000000u) && P.bvh_depth < S.K.STACK_SIZE && P.bvh_depth < WGPT_MAX_STACK;
+        const float box_tmin = restricted ? fmaxf(WGPT_RAY_TMIN, h4.y * 0.9999f) : WGPT_RAY_TMIN;
+        const bool hit = hit_bvh_binary(S, ray, nullptr, oc, closest, h, box_tmin) | hit_a;
+        P.pool.hit[slot] = make_float4(h.t, h.uu, h.vv, 0.0f);
+        const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
+        P.pool.hid[slot] = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
+        if (P.prim_type) {
+            const uint4 misc = P.pool.misc[slot];
+            if (misc.w == 0u) write_probe(S, P, misc.y, hit, h);
+        }
+    }
 }
 
 // after shade: publish the next ray queue, find frames that completed, advance the ring window
@@ -224,6 +259,7 @@ __global__ void k_wf_ctl_end(WfParams P) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     WfControl* c = P.ctl;
     c->n_extend = c->n_next; c->n_next = 0; c->extend_cursor = 0;
+    c->fallbacks += c->n_fallback; c->n_fallback = 0;
     uint32_t n_ready = 0;
     while (c->acc_k + n_ready < c->n_frames && n_ready < P.ring &&
            c->done[(c->acc_k + n_ready) % P.ring] == P.items_per_frame) {
@@ -263,7 +299,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     __shared__ uint32_t s_qn, s_arrived;
     WfControl* ctl = P.ctl;
     if (ctl->finished) return;                             // the host notices the flag one batch late: those launches are empty
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31u;
     if (threadIdx.x < WF_MAX_RING) s_done[threadIdx.x] = 0;
     if (threadIdx.x == 0) { s_qn = 0; s_arrived = 0; }
 
@@ -519,6 +555,7 @@ void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams
     if (ev) cudaEventRecord(ev[0], stream);
     if (S.counters) k_wf_extend<true><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
+    k_wf_fallback<<<148, 128, 0, stream>>>(S, P);
     if (ev) cudaEventRecord(ev[1], stream);
     const unsigned shade_blocks = (P.pool.capacity + WF_SHADE_THREADS - 1u) / WF_SHADE_THREADS;
     if (S.counters) k_wf_shade<true><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P);
