@@ -113,7 +113,7 @@ static int ensure_pool(wgpt_ctx* c) {
     uint32_t ring = (uint32_t)env_int("WGPT_RING", 64);
     ring = std::max(2u, std::min<uint32_t>(ring, WF_MAX_RING));
     // one allocation, carved into 16-byte-aligned arrays
-    const size_t per_slot = 8 * 16 + 4 + 4;
+    const size_t per_slot = 8 * 16 + 4;
     const size_t bytes = (size_t)cap * per_slot + (size_t)ring * npix * 16 + 32 * 256;
     cudaError_t e;
     if ((e = cudaMalloc(&F->pool_mem, bytes)) != cudaSuccess) return cuda_err(c, e, "wavefront pool alloc");
@@ -129,7 +129,6 @@ static int ensure_pool(wgpt_ctx* c) {
     P.pool.hid = (int4*)carve((size_t)cap * 16);   P.pool.misc = (uint4*)carve((size_t)cap * 16);
     P.pool.capacity = cap;
     P.q_extend = (uint32_t*)carve((size_t)cap * 4);
-    P.q_fallback = (uint32_t*)carve((size_t)cap * 4);
     P.stage = (float4*)carve((size_t)ring * npix * 16);
     P.ring = ring;
     P.items_per_frame = c->shard_pixels;

@@ -40,7 +40,7 @@ __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
         c->total_work = (unsigned long long)n_frames * P.items_per_frame;
         const unsigned long long win = (unsigned long long)P.ring * P.items_per_frame;
         c->work_limit = win < c->total_work ? win : c->total_work;
-        c->n_extend = 0; c->extend_cursor = 0; c->n_next = 0; c->n_fallback = 0;
+        c->n_extend = 0; c->extend_cursor = 0; c->n_next = 0;
         for (int k = 0; k < WF_MAX_RING; k++) c->done[k] = 0;
         c->acc_k = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
         c->finished = n_frames == 0 ? 1u : 0u; c->fallbacks = 0; c->iterations = 0;
@@ -187,12 +187,12 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
             if (has && tm == 0u && !(G.y & 0xff000000u) && sp == 0) {
                 if (ambiguous | tie) {
                     // equal-distance triangles or a stack overflow: the reference-order walk decides.  The slot
-                    // still holds the ray and its sphere/quad result, so it is only queued here and resolved by
-                    // k_wf_fallback with full warps (inline, one such ray stalled the other 31 lanes).
-                    // A tie (two triangles at exactly the closest distance; the reference keeps the one it visits
-                    // last) carries that distance along, an overflow of the wide stack does not.
-                    if (tie) reinterpret_cast<float*>(&P.pool.hit[slot])[1] = closest;
-                    P.q_fallback[atomicAdd(&ctl->n_fallback, 1u)] = slot | (tie ? 0x80000000u : 0u);
+                    // still holds the ray and its sphere/quad result; it is only MARKED here and the shade stage
+                    // resolves it (inline, one such ray stalled the other 31 lanes of this warp for the length
+                    // of a latency-bound binary walk; in shade the other warps of the SM hide that latency).
+                    // A tie carries the closest distance along, an overflow of the wide stack does not.
+                    if (!ambiguous) reinterpret_cast<float*>(&P.pool.hit[slot])[1] = closest;
+                    reinterpret_cast<int*>(&P.pool.hid[slot])[3] = ambiguous ? WF_CLS_OVERFLOW : WF_CLS_TIE;
                 } else {
                     const bool hit = hit_a | hit_t;
                     P.pool.hit[slot] = make_float4(h.t, h.uu, h.vv, 0.0f);
@@ -222,44 +222,11 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
     }
 }
 
-// Rays the wide walk could not decide (queued by k_wf_extend), re-traced with the reference-order
-// binary walk (hitRay.wgsl:42-110), one ray per thread.
-__global__ void __launch_bounds__(128) k_wf_fallback(DeviceScene S, WfParams P) {
-    WfControl* ctl = P.ctl;
-    const uint32_t n = ctl->n_fallback;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t entry = P.q_fallback[i];
-        const uint32_t slot = entry & 0x7fffffffu;
-        const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot], h4 = P.pool.hit[slot];
-        const int4 hid = P.pool.hid[slot];
-        Ray ray; ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
-        HitLite h; h.t = h4.x; h.uu = 0.0f; h.vv = 0.0f; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
-        const bool hit_a = hid.x != HIT_NONE;
-        float closest = hit_a ? h4.x : WGPT_MAX_FLOAT;
-        ObjRayCache oc; oc.reset();
-        // Tie with known closest distance D = h4.y: every triangle at distance D lies in nodes whose slab
-        // interval reaches D, and the reference reaches those nodes in the same order whatever else it
-        // visits, so the walk only needs the nodes overlapping [D(1 - 1e-4), closest].  (Not when the
-        // reference's stack guard could fire: its abort depends on everything visited.)
-        const bool restricted = (entry & 0x80000000u) && P.bvh_depth < S.K.STACK_SIZE && P.bvh_depth < WGPT_MAX_STACK;
-        const float box_tmin = restricted ? fmaxf(WGPT_RAY_TMIN, h4.y * 0.9999f) : WGPT_RAY_TMIN;
-        const bool hit = hit_bvh_binary(S, ray, nullptr, oc, closest, h, box_tmin) | hit_a;
-        P.pool.hit[slot] = make_float4(h.t, h.uu, h.vv, 0.0f);
-        const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
-        P.pool.hid[slot] = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
-        if (P.prim_type) {
-            const uint4 misc = P.pool.misc[slot];
-            if (misc.w == 0u) write_probe(S, P, misc.y, hit, h);
-        }
-    }
-}
-
 // after shade: publish the next ray queue, find frames that completed, advance the ring window
 __global__ void k_wf_ctl_end(WfParams P) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     WfControl* c = P.ctl;
     c->n_extend = c->n_next; c->n_next = 0; c->extend_cursor = 0;
-    c->fallbacks += c->n_fallback; c->n_fallback = 0;
     uint32_t n_ready = 0;
     while (c->acc_k + n_ready < c->n_frames && n_ready < P.ring &&
            c->done[(c->acc_k + n_ready) % P.ring] == P.items_per_frame) {
@@ -333,8 +300,33 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     }
     const uint32_t j = s_perm[threadIdx.x];
     const uint32_t slot = block_base + j;
-    const int4 hid = s_hid[j];
-    const int cls = hid.w;
+    int4 hid = s_hid[j];
+    int cls = hid.w;
+    float4 h4_resolved = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (cls >= WF_CLS_TIE) {
+        // ---- tie resolver: closest hit in reference order (hitRay.wgsl:42-110) for the rays extend marked ----
+        const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot], h4 = P.pool.hit[slot];
+        Ray r; r.o = V3(o4.x, o4.y, o4.z); r.d = V3(d4.x, d4.y, d4.z);
+        HitLite h; h.t = h4.x; h.uu = 0.0f; h.vv = 0.0f; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
+        const bool hit_a = hid.x != HIT_NONE;
+        float closest = hit_a ? h4.x : WGPT_MAX_FLOAT;
+        ObjRayCache oc; oc.reset();
+        // Tie with known closest distance D = h4.y: every triangle at distance D lies in nodes whose slab
+        // interval reaches D, and the reference reaches those nodes in the same order whatever else it
+        // visits, so the walk only needs the nodes overlapping [D(1 - 1e-4), closest].  (Not when the
+        // reference's stack guard could fire: its abort depends on everything visited.)
+        const bool restricted = cls == WF_CLS_TIE && P.bvh_depth < S.K.STACK_SIZE && P.bvh_depth < WGPT_MAX_STACK;
+        const float box_tmin = restricted ? fmaxf(WGPT_RAY_TMIN, h4.y * 0.9999f) : WGPT_RAY_TMIN;
+        const bool hit = hit_bvh_binary(S, r, nullptr, oc, closest, h, box_tmin) | hit_a;
+        cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
+        hid = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
+        h4_resolved = make_float4(h.t, h.uu, h.vv, 1.0f);
+        atomicAdd(&ctl->fallbacks, 1u);
+        if (P.prim_type) {
+            const uint4 misc = P.pool.misc[slot];
+            if (misc.w == 0u) write_probe(S, P, misc.y, hit, h);
+        }
+    }
 
     const uint32_t npix = (uint32_t)S.W * (uint32_t)S.H;
     const int side = S.K.STRATIFY ? strat_side(S) : 1;
@@ -360,7 +352,8 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
             acc = acc + V3(0.0f, 1.0f, 1.0f) * thr;
             ended = true;
         } else {
-            const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot], h4 = P.pool.hit[slot];
+            const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot];
+            const float4 h4 = h4_resolved.w != 0.0f ? h4_resolved : P.pool.hit[slot];
             ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
             HitLite h; h.t = h4.x; h.uu = h4.y; h.vv = h4.z; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
             ObjRayCache oc; oc.reset();
@@ -555,7 +548,6 @@ void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams
     if (ev) cudaEventRecord(ev[0], stream);
     if (S.counters) k_wf_extend<true><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
-    k_wf_fallback<<<148, 128, 0, stream>>>(S, P);
     if (ev) cudaEventRecord(ev[1], stream);
     const unsigned shade_blocks = (P.pool.capacity + WF_SHADE_THREADS - 1u) / WF_SHADE_THREADS;
     if (S.counters) k_wf_shade<true><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P);

@@ -18,7 +18,9 @@ namespace wg {
 #define WF_CLS_IDLE 5
 #define WF_CLS_DEAD 6
 #define WF_CLS_TRACE 7      // ray queued for the extend stage (which overwrites the class)
-#define WF_CLASSES 8
+#define WF_CLS_TIE 8        // extend found >= 2 triangles at exactly the closest distance: shade re-walks in reference order
+#define WF_CLS_OVERFLOW 9   // the wide stack overflowed: shade re-walks the whole reference tree
+#define WF_CLASSES 10
 
 // One path per slot, structure-of-arrays, 16-byte elements (LDG.128 / STG.128).
 struct PathPool {
@@ -40,7 +42,6 @@ struct WfControl {
     uint32_t n_extend;                 // rays queued for the extend stage of this iteration
     uint32_t extend_cursor;            // persistent-warp fetch cursor
     uint32_t n_next;                   // rays compacted by shade for the next iteration
-    uint32_t n_fallback;               // rays queued by extend for the reference-order walk (k_wf_fallback)
     uint32_t done[WF_MAX_RING];        // finished items per ring slot
     uint32_t acc_k;                    // next frame ordinal to fold into binding 3
     uint32_t ready_first, n_ready;     // frames the accumulate pass folds this iteration
@@ -54,7 +55,6 @@ struct WfParams {
     PathPool pool;
     WfControl* ctl;
     uint32_t* q_extend;                // slot ids of live rays, compacted by shade (capacity entries)
-    uint32_t* q_fallback;              // slot ids whose closest hit the reference-order walk must decide (capacity entries)
     float4* stage;                     // ring x W*H: (pixColor, 1)
     uint32_t ring;                     // frames in flight
     uint32_t items_per_frame;          // shard.n_pixels
@@ -71,7 +71,7 @@ void wf_launch_init(const WfParams& P, uint32_t n_frames, cudaStream_t stream);
 // ev: optional 4 events recorded before extend, after extend, after shade, after accumulate
 void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
                          cudaStream_t stream, cudaEvent_t* ev = nullptr);
-#define WF_LAUNCHES_PER_ITERATION 5
+#define WF_LAUNCHES_PER_ITERATION 4
 void launch_trace_rays_wide(const DeviceScene& S, const WideBvh& WB, int n, const float* rays, const uint32_t* seeds,
                             int* out_type, int* out_index, float* out_t, uint32_t* fallbacks, cudaStream_t stream);
 
