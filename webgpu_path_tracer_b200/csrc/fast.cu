@@ -9,6 +9,7 @@
 #include "context.h"
 #include "kernels.cuh"
 #include "wavefront.cuh"
+#include "bvh_build.cuh"
 
 namespace wg {
 
@@ -16,6 +17,9 @@ struct FastState {
     // wide BVH
     uint4* wide_nodes = nullptr; float4* wide_tris = nullptr; uint32_t* wide_scratch = nullptr;
     uint32_t wide_cap = 0, wide_tri_cap = 0;
+    // device-built hierarchy (K5, bvh_build.cu) that feeds K2 instead of binding 9
+    BvhNode* own_bvh = nullptr; void* build_scratch = nullptr; uint32_t own_cap = 0;
+    bool own_used = false;
     WideBuildStats wstats = {0, 0, 0, 0};
     // wavefront
     WfParams P;
@@ -86,12 +90,37 @@ static int ensure_wide(wgpt_ctx* c) {
         if (!F->wide_ev[0]) { cudaEventCreate(&F->wide_ev[0]); cudaEventCreate(&F->wide_ev[1]); }
         cudaEventRecord(F->wide_ev[0], c->stream);
     }
-    launch_wide_build((const BvhNode*)c->dbuf[9], n_bvh, (const Triangle*)c->dbuf[5], n_tri, F->wide_nodes, F->wide_tris,
-                      F->wide_cap, F->wide_scratch, c->stream);
-    c->last_launches += 1 + 2 * 48;
+    // Which hierarchy K2 flattens: by default one built here on the device from the triangles of
+    // binding 5 (K5: better surface-area quality than the reference's median split); WGPT_BVH=reference
+    // flattens binding 9 itself.  Binding 9 always remains the tree of exact mode and of the tie resolver.
+    const char* which = getenv("WGPT_BVH");
+    bool own = !(which && which[0] == 'r') && n_tri > 0 && n_bvh == 2 * n_tri - 1 && c->dbytes[6] && c->dbytes[7];
+    for (int attempt = 0; attempt < 2; attempt++) {
+        const BvhNode* src = (const BvhNode*)c->dbuf[9];
+        if (own) {
+            if ((uint32_t)n_tri > F->own_cap) {
+                if (F->own_bvh) cudaFree(F->own_bvh);
+                if (F->build_scratch) cudaFree(F->build_scratch);
+                F->own_bvh = nullptr; F->build_scratch = nullptr; F->own_cap = 0;
+                if ((e = cudaMalloc((void**)&F->own_bvh, (size_t)(2 * n_tri) * sizeof(BvhNode))) != cudaSuccess ||
+                    (e = cudaMalloc(&F->build_scratch, bvh_build_scratch_bytes(n_tri))) != cudaSuccess) return cuda_err(c, e, "bvh build alloc");
+                F->own_cap = (uint32_t)n_tri;
+            }
+            launch_bvh_build((const Triangle*)c->dbuf[5], n_tri, (const Mesh*)c->dbuf[6], (const ModelTransform*)c->dbuf[7],
+                             F->own_bvh, F->build_scratch, c->stream);
+            c->last_launches += BVH_BUILD_LAUNCHES;
+            src = F->own_bvh;
+        }
+        launch_wide_build(src, n_bvh, (const Triangle*)c->dbuf[5], n_tri, F->wide_nodes, F->wide_tris,
+                          F->wide_cap, F->wide_scratch, c->stream);
+        c->last_launches += 1 + 2 * 48;
+        F->wstats = wide_build_stats(F->wide_scratch, c->stream);
+        if ((e = cudaGetLastError()) != cudaSuccess) return cuda_err(c, e, "wide bvh build");
+        F->own_used = own;
+        if (!(F->wstats.overflow || F->wstats.n_tris != (uint32_t)n_tri) || !own) break;
+        own = false;                        // a degenerate clustering (too deep for K2): flatten the reference's tree instead
+    }
     if (c->stage_profiling) { cudaEventRecord(F->wide_ev[1], c->stream); F->wide_timed = true; }
-    F->wstats = wide_build_stats(F->wide_scratch, c->stream);
-    if ((e = cudaGetLastError()) != cudaSuccess) return cuda_err(c, e, "wide bvh build");
     if (F->wstats.overflow || F->wstats.n_tris != (uint32_t)n_tri)
         return set_err(c, WGPT_E_INVALID, "binary BVH does not meet the flatten contract (pre-order, 1-triangle leaves, depth <= 48 wide levels)");
     c->wide_dirty = false;
@@ -252,6 +281,8 @@ void fast_destroy(wgpt_ctx* c) {
     if (F->wide_nodes) cudaFree(F->wide_nodes);
     if (F->wide_tris) cudaFree(F->wide_tris);
     if (F->wide_scratch) cudaFree(F->wide_scratch);
+    if (F->own_bvh) cudaFree(F->own_bvh);
+    if (F->build_scratch) cudaFree(F->build_scratch);
     if (F->pool_mem) cudaFree(F->pool_mem);
     if (F->h_flag) cudaFreeHost(F->h_flag);
     if (F->flag_ev[0]) cudaEventDestroy(F->flag_ev[0]);
