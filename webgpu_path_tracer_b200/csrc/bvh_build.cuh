@@ -25,6 +25,6 @@ size_t bvh_build_scratch_bytes(int n_tris);
 // read back.  d_scratch must hold bvh_build_scratch_bytes(n_tris) bytes.
 void launch_bvh_build(const Triangle* tris, int n_tris, const Mesh* meshes, const ModelTransform* transforms,
                       BvhNode* out_nodes, void* d_scratch, cudaStream_t stream);
-#define BVH_BUILD_LAUNCHES 160
+#define BVH_BUILD_LAUNCHES 118   /* our kernels per build (the cub radix sort passes are not counted) */
 
 }  // namespace wg

@@ -267,7 +267,7 @@ int fast_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]) {
         float t = 0;
         cudaEventSynchronize(F->wide_ev[1]);
         cudaEventElapsedTime(&t, F->wide_ev[0], F->wide_ev[1]);
-        F->prof_ms[3] += t; F->prof_launches[3] += 1 + 2 * 48; F->wide_timed = false;
+        F->prof_ms[3] += t; F->prof_launches[3] += 1 + 2 * 48 + (F->own_used ? BVH_BUILD_LAUNCHES : 0); F->wide_timed = false;
     }
     for (int i = 0; i < 4; i++) { ms[i] = (float)F->prof_ms[i]; launches[i] = F->prof_launches[i]; F->prof_ms[i] = 0; F->prof_launches[i] = 0; }
     return WGPT_OK;
