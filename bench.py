@@ -292,22 +292,40 @@ def main():
         peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    ext_ms, ext_n = stage["extend"]
+    # Two kernels carry the step.  Algorithmic bytes:
+    #   extend: B_ray per closest-hit query, defined on the REFERENCE's traversal;
+    #   shade : B_shade = 224 B per path-bounce (the 7 x 16-byte state records of a slot, read once and
+    #           written once) + 48 B per finished sample (pixel sum read, pixel sum / staging-ring write).
+    # `roofline` is the kernel with the larger share of the step; the other one is reported beside it.
+    traffic_all = {}
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        traffic_all = json.load(open(tp)).get(args.config, {})
     rays_per_step_rank = (W * H * spp * F) * ref["rays_per_sample"]
-    alg_bytes_rank = rays_per_step_rank * ref["B_ray"] * args.steps          # this rank, K steps
-    roofline = None
-    if ext_n and ext_ms > 0:
-        achieved = alg_bytes_rank / (ext_ms * 1e-3) / 1e9
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(args.config, {}).get("extend_dram_bytes_per_launch")
-        roofline = {"bound": "hbm", "kernel": "k_wf_extend", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": alg_bytes_rank / ext_n, "avg_launch_ms": ext_ms / ext_n,
-                    "launches": ext_n, "share_of_step": ext_ms / total_ms,
-                    "B_ray": ref["B_ray"], "B_sample": ref["B_sample"], "rays_per_sample": ref["rays_per_sample"],
-                    "stage_ms": {k: v[0] for k, v in stage.items()}}
+    samples_per_step_rank = W * H * spp * F
+
+    def stage_roofline(kernel, key, alg_bytes_rank):
+        ms, n = stage[key]
+        if not n or ms <= 0:
+            return None
+        achieved = alg_bytes_rank / (ms * 1e-3) / 1e9
+        return {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic_all.get(key + "_dram_bytes_per_launch"), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg_bytes_rank / n, "avg_launch_ms": ms / n, "launches": n,
+                "share_of_step": ms / total_ms}
+
+    B_SHADE_BOUNCE, B_SHADE_SAMPLE = 224.0, 48.0
+    r_ext = stage_roofline("k_wf_extend", "extend", rays_per_step_rank * ref["B_ray"] * args.steps)
+    r_shd = stage_roofline("k_wf_shade", "shade",
+                           (rays_per_step_rank * B_SHADE_BOUNCE + samples_per_step_rank * B_SHADE_SAMPLE) * args.steps)
+    both = [r for r in (r_ext, r_shd) if r]
+    roofline = max(both, key=lambda r: r["share_of_step"]) if both else None
+    if roofline:
+        roofline = dict(roofline)
+        roofline.update({"B_ray": ref["B_ray"], "B_sample": ref["B_sample"], "rays_per_sample": ref["rays_per_sample"],
+                         "B_shade_per_bounce": B_SHADE_BOUNCE, "B_shade_per_sample": B_SHADE_SAMPLE,
+                         "stage_ms": {k: v[0] for k, v in stage.items()},
+                         "other_kernel": [r for r in both if r["kernel"] != roofline["kernel"]]})
 
     # ---------------- CPU baseline (oracle, bounded sample) ----------------
     cpu = None
@@ -329,7 +347,8 @@ def main():
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": CONFIG_DESC[args.config], "frames_per_step_per_gpu": F, "mode": args.mode,
                        "parallelism": "frame-strata x%d + ncclReduce(sum)" % world if world > 1 else "single GPU",
-                       "l2": "flushed between timed steps (256 MB device memset); the scene itself (<= 60 MB) is meant to live in L2"},
+                       "l2": "flushed between timed steps (256 MB device memset); the scene itself (<= 60 MB) is meant to live in L2",
+                       "hierarchy": "device-built (K5 PLOC) wide BVH" if os.environ.get("WGPT_BVH", "d")[0] != "r" else "reference tree flattened"},
             "Mrays_per_s": value * ref["rays_per_sample"],
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},

@@ -142,7 +142,7 @@ static int ensure_pool(wgpt_ctx* c) {
     uint32_t ring = (uint32_t)env_int("WGPT_RING", 64);
     ring = std::max(2u, std::min<uint32_t>(ring, WF_MAX_RING));
     // one allocation, carved into 16-byte-aligned arrays
-    const size_t per_slot = 8 * 16 + 4;
+    const size_t per_slot = WF_BYTES_PER_SLOT;
     const size_t bytes = (size_t)cap * per_slot + (size_t)ring * npix * 16 + 32 * 256;
     cudaError_t e;
     if ((e = cudaMalloc(&F->pool_mem, bytes)) != cudaSuccess) return cuda_err(c, e, "wavefront pool alloc");
@@ -152,10 +152,9 @@ static int ensure_pool(wgpt_ctx* c) {
     WfParams& P = F->P;
     memset(&P, 0, sizeof(P));
     P.ctl = (WfControl*)carve(sizeof(WfControl));
-    P.pool.ro = (float4*)carve((size_t)cap * 16);  P.pool.rd = (float4*)carve((size_t)cap * 16);
-    P.pool.thr = (float4*)carve((size_t)cap * 16); P.pool.acc = (float4*)carve((size_t)cap * 16);
-    P.pool.pix = (float4*)carve((size_t)cap * 16); P.pool.hit = (float4*)carve((size_t)cap * 16);
-    P.pool.hid = (int4*)carve((size_t)cap * 16);   P.pool.misc = (uint4*)carve((size_t)cap * 16);
+    P.pool.e0 = (float4*)carve((size_t)cap * 16); P.pool.e1 = (float4*)carve((size_t)cap * 16);
+    P.pool.s0 = (float4*)carve((size_t)cap * 16); P.pool.s1 = (float4*)carve((size_t)cap * 16);
+    P.pool.s2 = (float4*)carve((size_t)cap * 16); P.pool.pix = (float4*)carve((size_t)cap * 16);
     P.pool.capacity = cap;
     P.q_extend = (uint32_t*)carve((size_t)cap * 4);
     P.stage = (float4*)carve((size_t)ring * npix * 16);
@@ -187,6 +186,8 @@ static int check_materials(wgpt_ctx* c) {
 int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_first, int* d_ptype, int* d_pindex, float* d_pt) {
     int rc = check_materials(c);
     if (rc) return rc;
+    if (c->cfg.max_bounces > WF_MAX_BOUNCE_FIELD || c->cfg.num_samples > 65535)
+        return set_err(c, WGPT_E_INVALID, "fast mode packs the bounce / sample counters: max_bounces <= 1023, num_samples <= 65535");
     if ((rc = ensure_wide(c)) != WGPT_OK) return rc;
     if ((rc = ensure_pool(c)) != WGPT_OK) return rc;
     FastState* F = c->fast;

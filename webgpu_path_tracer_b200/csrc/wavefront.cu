@@ -33,7 +33,7 @@ __device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0,
 
 __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < P.pool.capacity) P.pool.hid[i] = make_int4(HIT_NONE, -1, -1, WF_CLS_IDLE);
+    if (i < P.pool.capacity) P.pool.e1[i] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_tag(HIT_NONE, WF_CLS_IDLE, -1)));
     if (i == 0) {
         WfControl* c = P.ctl;
         c->next_work = 0;
@@ -99,6 +99,7 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
     h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1;
     float closest = WGPT_MAX_FLOAT;
     bool hit_t = false, hit_a = false, ambiguous = false, tie = false;
+    uint32_t tag0 = 0;           // tag of the slot as shade left it (kind / material of the sphere-quad hit)
     uint2 G = make_uint2(0u, 0u);
     uint32_t tm = 0, tri_base = 0, tri_lmask = 0;   // parked candidate triangles of the last node visited: hit leaf slots, first
                                                     // packed triangle, leaf-slot mask (triangle of slot b = tri_base + popc(lmask below b))
@@ -119,13 +120,14 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     const uint32_t idx = base + (uint32_t)__popc(m & lanemask_lt());
                     if (idx < n) {
                         slot = P.q_extend[idx];
-                        const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot], h4 = P.pool.hit[slot];
-                        const int4 hid = P.pool.hid[slot];
+                        const float4 o4 = P.pool.e0[slot], d4 = P.pool.e1[slot];
+                        tag0 = __float_as_uint(d4.w);
                         ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
-                        // sphere/quad result carried in by shade
-                        h.t = h4.x; h.uu = 0.0f; h.vv = 0.0f; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
-                        hit_a = hid.x != HIT_NONE;
-                        closest = hit_a ? h4.x : WGPT_MAX_FLOAT;
+                        // sphere/quad result carried in by shade; its index stays in the slot (s2.y), which
+                        // this stage only overwrites when a triangle wins
+                        h.t = o4.w; h.uu = 0.0f; h.vv = 0.0f; h.kind = wf_tag_kind(tag0); h.index = -1; h.mat_id = wf_tag_mat(tag0);
+                        hit_a = h.kind != HIT_NONE;
+                        closest = hit_a ? o4.w : WGPT_MAX_FLOAT;
                         oc.reset();
                         hit_t = false; ambiguous = false; tie = false; sp = 0; tm = 0;
                         wr = make_wide_ray(ray);
@@ -191,16 +193,25 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     // resolves it (inline, one such ray stalled the other 31 lanes of this warp for the length
                     // of a latency-bound binary walk; in shade the other warps of the SM hide that latency).
                     // A tie carries the closest distance along, an overflow of the wide stack does not.
-                    if (!ambiguous) reinterpret_cast<float*>(&P.pool.hit[slot])[1] = closest;
-                    reinterpret_cast<int*>(&P.pool.hid[slot])[3] = ambiguous ? WF_CLS_OVERFLOW : WF_CLS_TIE;
+                    if (!ambiguous) reinterpret_cast<float*>(&P.pool.s2[slot])[2] = closest;
+                    reinterpret_cast<uint32_t*>(&P.pool.e1[slot])[3] = (tag0 & ~0xf0u) | ((uint32_t)(ambiguous ? WF_CLS_OVERFLOW : WF_CLS_TIE) << 4);
                 } else {
                     const bool hit = hit_a | hit_t;
-                    P.pool.hit[slot] = make_float4(h.t, h.uu, h.vv, 0.0f);
                     const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
-                    P.pool.hid[slot] = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
+                    uint32_t tag = (tag0 & ~0xf0u) | ((uint32_t)cls << 4);          // the sphere/quad hit (or the miss) stands
+                    if (hit_t) {
+                        tag = wf_tag(HIT_TRI, cls, h.mat_id);
+                        float* e0 = reinterpret_cast<float*>(&P.pool.e0[slot]);
+                        float* s2 = reinterpret_cast<float*>(&P.pool.s2[slot]);
+                        e0[3] = h.t; s2[1] = __int_as_float(h.index); s2[2] = h.uu; s2[3] = h.vv;
+                    }
+                    reinterpret_cast<uint32_t*>(&P.pool.e1[slot])[3] = tag;
                     if (P.prim_type) {
-                        const uint4 misc = P.pool.misc[slot];
-                        if (misc.w == 0u) write_probe(S, P, misc.y, hit, h);     // first query of the item: the primary ray
+                        const float4 s1v = P.pool.s1[slot], s2v = P.pool.s2[slot];
+                        if ((__float_as_uint(s2v.x) & 0x03ffffffu) == 0u) {                // first query of the item: the primary ray
+                            if (!hit_t) h.index = __float_as_int(s2v.y);
+                            write_probe(S, P, __float_as_uint(s1v.w), hit, h);
+                        }
                     }
                 }
                 has = false;
@@ -260,7 +271,7 @@ template <bool COUNT>
 __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(DeviceScene S, WfParams P) {
     __shared__ uint32_t s_done[WF_MAX_RING];
     __shared__ uint32_t s_key_cnt[32];                 // slots per shade key
-    __shared__ int4 s_hid[WF_SHADE_THREADS];
+    __shared__ float4 s_e1[WF_SHADE_THREADS];           // (ray direction, tag) of the block's slots
     __shared__ uint32_t s_perm[WF_SHADE_THREADS];
     __shared__ uint32_t s_q[WF_SHADE_THREADS];          // slot ids for the next ray queue
     __shared__ uint32_t s_qn, s_arrived;
@@ -278,10 +289,11 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     if (threadIdx.x < 32) s_key_cnt[threadIdx.x] = 0;
     {
         const uint32_t s0 = block_base + threadIdx.x;
-        int4 hid = make_int4(HIT_NONE, -1, -1, WF_CLS_DEAD);
-        if (s0 < P.pool.capacity) hid = P.pool.hid[s0];
-        s_hid[threadIdx.x] = hid;
-        const uint32_t key = hid.w < WF_CLS_MISS ? (uint32_t)(hid.w * 4 + (hid.x & 3)) : (uint32_t)(12 + hid.w);
+        float4 e1v = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_tag(HIT_NONE, WF_CLS_DEAD, -1)));
+        if (s0 < P.pool.capacity) e1v = P.pool.e1[s0];
+        s_e1[threadIdx.x] = e1v;
+        const int cls0 = wf_tag_cls(__float_as_uint(e1v.w)), kind0 = wf_tag_kind(__float_as_uint(e1v.w));
+        const uint32_t key = cls0 < WF_CLS_MISS ? (uint32_t)(cls0 * 4 + (kind0 & 3)) : (uint32_t)(12 + cls0);
         const uint32_t peers = __match_any_sync(0xffffffffu, key);
         const int leader = __ffs((int)peers) - 1;
         __syncthreads();
@@ -300,31 +312,34 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     }
     const uint32_t j = s_perm[threadIdx.x];
     const uint32_t slot = block_base + j;
-    int4 hid = s_hid[j];
+    const float4 e1v = s_e1[j];
+    // (hit kind, hit index, material id, shade class) of the slot
+    int4 hid = make_int4(wf_tag_kind(__float_as_uint(e1v.w)), -1, wf_tag_mat(__float_as_uint(e1v.w)), wf_tag_cls(__float_as_uint(e1v.w)));
     int cls = hid.w;
     float4 h4_resolved = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    bool resolved = false;
     if (cls >= WF_CLS_TIE) {
         // ---- tie resolver: closest hit in reference order (hitRay.wgsl:42-110) for the rays extend marked ----
-        const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot], h4 = P.pool.hit[slot];
-        Ray r; r.o = V3(o4.x, o4.y, o4.z); r.d = V3(d4.x, d4.y, d4.z);
-        HitLite h; h.t = h4.x; h.uu = 0.0f; h.vv = 0.0f; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
+        const float4 o4 = P.pool.e0[slot], s2v = P.pool.s2[slot];
+        Ray r; r.o = V3(o4.x, o4.y, o4.z); r.d = V3(e1v.x, e1v.y, e1v.z);
+        HitLite h; h.t = o4.w; h.uu = 0.0f; h.vv = 0.0f; h.kind = hid.x; h.index = __float_as_int(s2v.y); h.mat_id = hid.z;
         const bool hit_a = hid.x != HIT_NONE;
-        float closest = hit_a ? h4.x : WGPT_MAX_FLOAT;
+        float closest = hit_a ? o4.w : WGPT_MAX_FLOAT;
         ObjRayCache oc; oc.reset();
         // Tie with known closest distance D = h4.y: every triangle at distance D lies in nodes whose slab
         // interval reaches D, and the reference reaches those nodes in the same order whatever else it
         // visits, so the walk only needs the nodes overlapping [D(1 - 1e-4), closest].  (Not when the
         // reference's stack guard could fire: its abort depends on everything visited.)
         const bool restricted = cls == WF_CLS_TIE && P.bvh_depth < S.K.STACK_SIZE && P.bvh_depth < WGPT_MAX_STACK;
-        const float box_tmin = restricted ? fmaxf(WGPT_RAY_TMIN, h4.y * 0.9999f) : WGPT_RAY_TMIN;
+        const float box_tmin = restricted ? fmaxf(WGPT_RAY_TMIN, s2v.z * 0.9999f) : WGPT_RAY_TMIN;
         const bool hit = hit_bvh_binary(S, r, nullptr, oc, closest, h, box_tmin) | hit_a;
         cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
         hid = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
         h4_resolved = make_float4(h.t, h.uu, h.vv, 1.0f);
+        resolved = true;
         atomicAdd(&ctl->fallbacks, 1u);
         if (P.prim_type) {
-            const uint4 misc = P.pool.misc[slot];
-            if (misc.w == 0u) write_probe(S, P, misc.y, hit, h);
+            if ((__float_as_uint(s2v.x) & 0x03ffffffu) == 0u) write_probe(S, P, __float_as_uint(P.pool.s1[slot].w), hit, h);
         }
     }
 
@@ -333,7 +348,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     const uint32_t samples_per_item = S.K.STRATIFY ? (uint32_t)(side * side) : (uint32_t)S.K.NUM_SAMPLES;
 
     bool alive = false, need_work = false, store_pix = false, gen = false;
-    uint32_t rng = 0, pix_i = 0, frame_k = 0, bounce = 0, scnt = 0, gen_pixel = 0;
+    uint32_t rng = 0, pix_i = 0, ring_slot = 0, frame_k = 0, bounce = 0, scnt = 0, gen_pixel = 0;
     unsigned n_samples = 0, n_draws = 0;
     Counts cnt = {0, 0, 0, 0, 0, 0, 0, 0};
     Ray ray; ray.o = ray.d = V3s(0.0f);
@@ -344,18 +359,19 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         need_work = true;
     } else if (cls <= WF_CLS_MISS) {
         bool ended = false;
-        const uint4 misc = P.pool.misc[slot];
-        rng = misc.x; pix_i = misc.y; frame_k = misc.z; bounce = misc.w >> 16; scnt = misc.w & 0xffffu;
-        const float4 t4 = P.pool.thr[slot], a4 = P.pool.acc[slot];
-        thr = V3(t4.x, t4.y, t4.z); acc = V3(a4.x, a4.y, a4.z);
+        const float4 s0v = P.pool.s0[slot], s1v = P.pool.s1[slot], s2v = P.pool.s2[slot];
+        const uint32_t ctr = __float_as_uint(s2v.x);
+        rng = __float_as_uint(s1v.z); pix_i = __float_as_uint(s1v.w);
+        ring_slot = ctr >> 26; bounce = (ctr >> 16) & 0x3ffu; scnt = ctr & 0xffffu;
+        thr = V3(s0v.x, s0v.y, s0v.z); acc = V3(s0v.w, s1v.x, s1v.y);
         if (cls == WF_CLS_MISS) {                             // traceRay.wgsl:12-16
             acc = acc + V3(0.0f, 1.0f, 1.0f) * thr;
             ended = true;
         } else {
-            const float4 o4 = P.pool.ro[slot], d4 = P.pool.rd[slot];
-            const float4 h4 = h4_resolved.w != 0.0f ? h4_resolved : P.pool.hit[slot];
-            ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
-            HitLite h; h.t = h4.x; h.uu = h4.y; h.vv = h4.z; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
+            const float4 o4 = P.pool.e0[slot];
+            ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(e1v.x, e1v.y, e1v.z);
+            HitLite h; h.t = o4.w; h.uu = s2v.z; h.vv = s2v.w; h.kind = hid.x; h.index = __float_as_int(s2v.y); h.mat_id = hid.z;
+            if (resolved) { h.t = h4_resolved.x; h.uu = h4_resolved.y; h.vv = h4_resolved.z; h.index = hid.y; }
             ObjRayCache oc; oc.reset();
             ShadeState st;
             st.p = st.n = st.unit_w = st.u = st.v = V3s(0.0f);
@@ -379,8 +395,8 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
                 gen = true; gen_pixel = pixel;                             // next sample, same RNG stream
             } else {
                 const float div = S.K.STRATIFY ? pix.w : (float)S.K.NUM_SAMPLES;
-                P.stage[(size_t)(frame_k % P.ring) * npix + pixel] = make_float4(fd(pix.x, div), fd(pix.y, div), fd(pix.z, div), 1.0f);
-                atomicAdd(&s_done[frame_k % P.ring], 1u);
+                P.stage[(size_t)ring_slot * npix + pixel] = make_float4(fd(pix.x, div), fd(pix.y, div), fd(pix.z, div), 1.0f);
+                atomicAdd(&s_done[ring_slot], 1u);
                 need_work = true;
             }
         }
@@ -415,6 +431,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
                     if (rem < 0) { fk0--; rem += P.items_per_frame; }
                     while (rem >= (long long)P.items_per_frame) { fk0++; rem -= P.items_per_frame; }
                     frame_k = fk0;
+                    ring_slot = fk0 % P.ring;
                     pix_i = (uint32_t)rem;
                     const uint32_t pixel = shard_pixel(S.shard, S.W, pix_i);
                     const uint32_t lim_pix = npix < S.shard.pixel_limit ? npix : S.shard.pixel_limit;
@@ -425,7 +442,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
                         pix = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                         gen = true; gen_pixel = pixel;
                     } else {
-                        atomicAdd(&s_done[frame_k % P.ring], 1u);      // tile tail past the image: nothing to render
+                        atomicAdd(&s_done[ring_slot], 1u);             // tile tail past the image: nothing to render
                         new_cls = WF_CLS_IDLE;                         // try again next iteration
                     }
                 }
@@ -451,18 +468,16 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         const bool hit_a = hit_analytic(S, ray, rng, COUNT ? &cnt : nullptr, closest, h);
         trace = S.NUM_AABB > 0 && root_box_hit(S, ray, closest);
         const int ncls = trace ? WF_CLS_TRACE : (hit_a ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS);
-        const uint32_t miscw = (bounce << 16) | (scnt & 0xffffu);
-        P.pool.ro[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, 0.0f);
-        P.pool.rd[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.0f);
-        P.pool.thr[slot] = make_float4(thr.x, thr.y, thr.z, 0.0f);
-        P.pool.acc[slot] = make_float4(acc.x, acc.y, acc.z, 0.0f);
-        P.pool.misc[slot] = make_uint4(rng, pix_i, frame_k, miscw);
+        const uint32_t ctr = wf_ctr(ring_slot, bounce, scnt);
+        P.pool.e0[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, h.t);
+        P.pool.e1[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(wf_tag(hit_a ? h.kind : (int)HIT_NONE, ncls, h.mat_id)));
+        P.pool.s0[slot] = make_float4(thr.x, thr.y, thr.z, acc.x);
+        P.pool.s1[slot] = make_float4(acc.y, acc.z, __uint_as_float(rng), __uint_as_float(pix_i));
+        P.pool.s2[slot] = make_float4(__uint_as_float(ctr), __int_as_float(h.index), 0.0f, 0.0f);
         if (store_pix) P.pool.pix[slot] = pix;
-        P.pool.hit[slot] = make_float4(h.t, 0.0f, 0.0f, 0.0f);
-        P.pool.hid[slot] = make_int4(hit_a ? h.kind : (int)HIT_NONE, h.index, h.mat_id, ncls);
-        if (!trace && P.prim_type && miscw == 0u) write_probe(S, P, pix_i, hit_a, h);
+        if (!trace && P.prim_type && (ctr & 0x03ffffffu) == 0u) write_probe(S, P, pix_i, hit_a, h);
     } else if (cls <= WF_CLS_IDLE && new_cls != cls) {
-        P.pool.hid[slot].w = new_cls;               // idle (waiting for the window) or dead (no work left)
+        reinterpret_cast<uint32_t*>(&P.pool.e1[slot])[3] = wf_tag(HIT_NONE, new_cls, -1);    // idle (waiting for the window) or dead (no work left)
     }
 
     // ---- compact: rays that need the BVH into the next ray queue, one global atomic per block ----

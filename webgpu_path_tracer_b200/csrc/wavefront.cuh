@@ -22,18 +22,30 @@ namespace wg {
 #define WF_CLS_OVERFLOW 9   // the wide stack overflowed: shade re-walks the whole reference tree
 #define WF_CLASSES 10
 
-// One path per slot, structure-of-arrays, 16-byte elements (LDG.128 / STG.128).
+// One path per slot, structure-of-arrays, 16-byte records (LDG.128 / STG.128), 80 bytes per slot
+// + the 16-byte pixel sum that is only touched when a sample starts or ends.  The shade stage is
+// HBM-bound on exactly these bytes (it reads and rewrites every live slot once per bounce), so
+// the state is packed: no padding lanes, ids in one word.
+//   e0 = (ray origin.xyz, hit t)                      written by shade (t of the sphere/quad hit) and extend (final t)
+//   e1 = (ray direction.xyz, tag)                      tag = (material id << 8) | (shade class << 4) | (hit kind + 1)
+//   s0 = (throughput.xyz, radiance.x)
+//   s1 = (radiance.y, radiance.z, rng state, shard-local pixel)
+//   s2 = (counters, hit index, hit u, hit v)           counters = (ring slot << 26) | (bounce << 16) | sample
+//        For WF_CLS_TIE the u lane carries the closest distance the extend stage found.
+// The extend stage reads e0, e1 (32 B) and writes e0, e1 and the .yzw lanes of s2.
 struct PathPool {
-    float4* ro;      // ray origin.xyz
-    float4* rd;      // ray direction.xyz
-    float4* thr;     // throughput.xyz
-    float4* acc;     // accumulated radiance of the current sample .xyz
+    float4* e0; float4* e1; float4* s0; float4* s1; float4* s2;
     float4* pix;     // pixColor of the (pixel, frame) so far .xyz, .w = samples taken (stratified divisor)
-    float4* hit;     // t, uu, vv of the last closest-hit query
-    int4*   hid;     // kind (HitKind), index, mat_id, shade class (WF_CLS_*)
-    uint4*  misc;    // rng state, shard-local pixel i, frame ordinal k, (bounce << 16) | sample counter
     uint32_t capacity;
 };
+#define WF_BYTES_PER_SLOT (6 * 16 + 4)      /* 6 records + one ray-queue entry */
+#define WF_MAX_BOUNCE_FIELD 1023
+
+__host__ __device__ inline uint32_t wf_tag(int kind, int cls, int mat_id) { return ((uint32_t)mat_id << 8) | ((uint32_t)cls << 4) | (uint32_t)(kind + 1); }
+__host__ __device__ inline int wf_tag_kind(uint32_t tag) { return (int)(tag & 15u) - 1; }
+__host__ __device__ inline int wf_tag_cls(uint32_t tag) { return (int)((tag >> 4) & 15u); }
+__host__ __device__ inline int wf_tag_mat(uint32_t tag) { return (int)(tag >> 8) == 0xffffff ? -1 : (int)(tag >> 8); }
+__host__ __device__ inline uint32_t wf_ctr(uint32_t ring_slot, uint32_t bounce, uint32_t scnt) { return (ring_slot << 26) | (bounce << 16) | (scnt & 0xffffu); }
 
 struct WfControl {
     unsigned long long next_work;      // next (frame ordinal, pixel) item to hand out
