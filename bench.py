@@ -294,7 +294,7 @@ def main():
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     # Two kernels carry the step.  Algorithmic bytes:
     #   extend: B_ray per closest-hit query, defined on the REFERENCE's traversal;
-    #   shade : B_shade = 224 B per path-bounce (the 7 x 16-byte state records of a slot, read once and
+    #   shade : B_shade = 160 B per path-bounce (the 5 x 16-byte state records of a slot, read once and
     #           written once) + 48 B per finished sample (pixel sum read, pixel sum / staging-ring write).
     # `roofline` is the kernel with the larger share of the step; the other one is reported beside it.
     traffic_all = {}
@@ -314,7 +314,7 @@ def main():
                 "algorithmic_bytes_per_launch": alg_bytes_rank / n, "avg_launch_ms": ms / n, "launches": n,
                 "share_of_step": ms / total_ms}
 
-    B_SHADE_BOUNCE, B_SHADE_SAMPLE = 224.0, 48.0
+    B_SHADE_BOUNCE, B_SHADE_SAMPLE = 160.0, 48.0
     r_ext = stage_roofline("k_wf_extend", "extend", rays_per_step_rank * ref["B_ray"] * args.steps)
     r_shd = stage_roofline("k_wf_shade", "shade",
                            (rays_per_step_rank * B_SHADE_BOUNCE + samples_per_step_rank * B_SHADE_SAMPLE) * args.steps)
