@@ -124,6 +124,8 @@ def run_reference(args):
     from oracle.binding import Oracle
     scene, cam, W, H, kw = bench_scenes.build(args.config)
     okw = {k: v for k, v in kw.items()}
+    # every host thread the box has (torchrun exports OMP_NUM_THREADS=1 to its workers: do not inherit that)
+    okw["threads"] = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     orc = Oracle(W, H, **okw)
     orc.write_scene(scene.buffers())
     orc.write_uniforms(1, 0, cam.viewMatrix)
@@ -331,7 +333,7 @@ def main():
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         from oracle.binding import Oracle
-        orc = Oracle(W, H, **kw)
+        orc = Oracle(W, H, threads=len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1), **kw)
         orc.write_scene(bufs)
         orc.write_uniforms(1, 0, cam.viewMatrix)
         orc.render(1, 1)
