@@ -150,3 +150,24 @@ def test_coplanar_ties_resolve_like_the_reference_walk():
     tg, ig, dg = g.trace_rays(rays, seeds)
     assert int((te != tg).sum()) == 0 and int((ie != ig).sum()) == 0
     assert np.array_equal(bits(de), bits(dg))
+
+
+def test_renderer_mirror_saves_the_presented_image(default_scene, tmp_path):
+    """Renderer.renderFrames + save_image (N4): the file holds exactly wgpt_present's RGBA8 output, and the
+    reset semantics of renderAnimation (camera moving -> resetBuffer = 1, frameNum back to 1) hold in fast mode."""
+    from webgpu_path_tracer_b200 import Renderer, Scene, Camera, imageio
+    scene = Scene()
+    cam = Camera()
+    cam.set_camera([0.5, 0, 2.5], [0.5, 0, 0], [0, 1, 0])
+    r = Renderer.create(mode=MODE_FAST)
+    r.initBuffers(scene, cam, 96, 64)
+    r.setRenderParameters({}, cam, 96, 64)
+    r.renderFrames(4)
+    path = tmp_path / "frame.png"
+    rgba8 = r.save_image(path)
+    assert np.array_equal(imageio.decode_png(path.read_bytes()), rgba8[:, :, :3])
+    o = Oracle(96, 64)
+    o.write_scene(scene.buffers())
+    o.write_uniforms(1, 0, cam.viewMatrix)
+    o.render(1, 4)
+    assert np.array_equal(bits(o.read_framebuffer()), bits(r.webGPU.read_framebuffer()))

@@ -167,3 +167,18 @@ def test_product_package_never_imports_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle/" not in src.replace("oracle/ovec.h", "").replace("oracle/)", "") or f in ("api.py", "__init__.py", "pvec.cuh"), f
                 assert "import oracle" not in src and "from oracle" not in src, f
+
+
+def test_png_and_ppm_writers_round_trip(tmp_path):
+    """N4: the canvas is a file here; the PNG the host layer writes decodes back to the same pixels."""
+    from webgpu_path_tracer_b200 import imageio
+    rng = np.random.default_rng(3)
+    img = rng.random((37, 53, 4)).astype(np.float32)
+    want = np.clip(np.rint(img * 255.0), 0, 255).astype(np.uint8)
+    for alpha in (False, True):
+        got = imageio.decode_png(imageio.encode_png(img, alpha=alpha))
+        assert np.array_equal(got, want if alpha else want[:, :, :3])
+    p = tmp_path / "x.ppm"
+    imageio.write_ppm(p, img)
+    raw = p.read_bytes()
+    assert raw.startswith(b"P6\n53 37\n255\n") and raw[len(b"P6\n53 37\n255\n"):] == want[:, :, :3].tobytes()

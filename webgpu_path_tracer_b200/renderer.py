@@ -10,6 +10,7 @@ array: `last_image` holds what `fs` would have put on the canvas.
 import numpy as np
 
 from .api import PathTracer, MODE_EXACT, MODE_FAST
+from . import imageio
 
 
 class Renderer:
@@ -74,3 +75,9 @@ class Renderer:
     def present(self, rgba8=False):
         self.webGPU.write_uniforms(self.frameNum, 0, self.camera.viewMatrix)
         return self.webGPU.present(rgba8=rgba8)
+
+    def save_image(self, path):
+        """Write what the canvas would show (fs output, RGBA8) to a .png or .ppm file."""
+        rgba8 = np.asarray(self.present(rgba8=True)[1]).reshape(self.HEIGHT, self.WIDTH, 4)
+        (imageio.write_ppm if str(path).lower().endswith(".ppm") else imageio.write_png)(path, rgba8)
+        return rgba8
