@@ -139,12 +139,14 @@ int wgpt_fast_statistics(wgpt_ctx* ctx, wgpt_fast_stats* out);
 /* Per-stage device time of the fast path, for the roofline line of bench.py.  When enabled, every
  * extend / shade launch is bracketed by CUDA events on the context's stream (about 1 us each);
  * wgpt_stage_timings synchronises and returns the sums since it was last called:
- * ms[0] extend (K3 traversal), ms[1] shade, ms[2] control + accumulate (K4), ms[3] wide-BVH build (K2);
+ * ms[0] extend (K3 traversal), ms[1] shade, ms[2] control + accumulate (K4), ms[3] hierarchy build (K5 BVH build + K2 wide flatten);
  * launches[i] = kernel launches counted in ms[i]. */
 int wgpt_set_stage_profiling(wgpt_ctx* ctx, int enabled);
 int wgpt_stage_timings(wgpt_ctx* ctx, float ms[4], uint64_t launches[4]);
 
-/* pinned-math probe for tests: fn 0 sin, 1 cos, 2 acos, 3 log, 4 pow(x,y), evaluated ON THE GPU */
+/* pinned-math probe for tests: fn 0 sin, 1 cos, 2 acos, 3 log, 4 pow(x,y), evaluated ON THE GPU;
+ * 5 x/y through the shading code's shared-reciprocal vector division, 6 / 7 sin / cos through its
+ * one-reduction sincos (device-only forms that must equal the plain ones bit for bit) */
 int wgpt_pinned_math(wgpt_ctx* ctx, int fn, int n, const float* x, const float* y, float* out);
 
 #ifdef __cplusplus

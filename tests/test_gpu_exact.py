@@ -63,3 +63,30 @@ def test_default_scene_accumulation_and_present_bit_exact(default_scene):
     for x in (o, g):
         x.write_uniforms(4, 0, cam.viewMatrix)
     assert np.array_equal(bits(o.present()), bits(g.present()))
+
+
+def test_device_only_math_forms_equal_the_plain_ones():
+    """The shading code divides a vector by a scalar with ONE reciprocal refinement shared by the three
+    components, and evaluates sin and cos of an angle with one range reduction; both must produce the bits
+    of IEEE division / of the separate pinned functions."""
+    from oracle.binding import pinned_math
+    g = PathTracer(8, 8, mode=MODE_EXACT)
+    rng = np.random.default_rng(11)
+    n = 4_000_000
+    # numerators / divisors over many binades, plus the edge cases (zeros, denormals, huge, tiny, inf, nan)
+    x = (rng.standard_normal(n) * np.exp2(rng.integers(-70, 70, n))).astype(np.float32)
+    y = (np.abs(rng.standard_normal(n)) * np.exp2(rng.integers(-70, 70, n))).astype(np.float32)
+    edge = np.array([0.0, -0.0, 1e-45, -1e-45, 1e-38, 3e38, -3e38, np.inf, -np.inf, np.nan, 1.0, -1.0, 1e-19, 1e19], np.float32)
+    ex, ey = np.meshgrid(edge, edge)
+    x[:ex.size] = ex.ravel()
+    y[:ey.size] = ey.ravel()
+    # unit-length style operands, the common case in normalize()
+    x[1000:2_000_000] = rng.uniform(-1, 1, 2_000_000 - 1000).astype(np.float32)
+    y[1000:2_000_000] = rng.uniform(0.05, 2, 2_000_000 - 1000).astype(np.float32)
+    with np.errstate(all="ignore"):
+        want = (x / y).astype(np.float32)
+    got = g.pinned_math("vdiv", x, y)
+    assert np.array_equal(bits(got), bits(want))
+    a = (rng.uniform(-1, 1, 1_000_000) * 7.0).astype(np.float32)
+    assert np.array_equal(bits(g.pinned_math("sincos_sin", a)), bits(pinned_math("sin", a)))
+    assert np.array_equal(bits(g.pinned_math("sincos_cos", a)), bits(pinned_math("cos", a)))

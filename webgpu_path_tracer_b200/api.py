@@ -214,7 +214,7 @@ class PathTracer:
         return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(names)}
 
     def pinned_math(self, fn, x, y=None):
-        names = {"sin": 0, "cos": 1, "acos": 2, "log": 3, "pow": 4}
+        names = {"sin": 0, "cos": 1, "acos": 2, "log": 3, "pow": 4, "vdiv": 5, "sincos_sin": 6, "sincos_cos": 7}
         x = np.ascontiguousarray(x, np.float32)
         y = np.ascontiguousarray(y, np.float32) if y is not None else None
         out = np.empty_like(x)

@@ -234,7 +234,7 @@ int wgpt_last_timing(wgpt_ctx* c, float* ms, uint64_t* launches) {
 }
 
 int wgpt_pinned_math(wgpt_ctx* c, int fn, int n, const float* x, const float* y, float* out) {
-    if (!c || n < 0 || (n && (!x || !out)) || fn < 0 || fn > 4) return WGPT_E_INVALID;
+    if (!c || n < 0 || (n && (!x || !out)) || fn < 0 || fn > 7) return WGPT_E_INVALID;
     if (n == 0) return WGPT_OK;
     cudaSetDevice(c->cfg.device);
     HostScratch dx, dy, dout;

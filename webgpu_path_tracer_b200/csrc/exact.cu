@@ -141,7 +141,11 @@ __global__ void k_pinned_math(int fn, int n, const float* x, const float* y, flo
         case 1: out[i] = wgpt_pm::cosf_(x[i]); break;
         case 2: out[i] = wgpt_pm::acosf_(x[i]); break;
         case 3: out[i] = wgpt_pm::logf_(x[i]); break;
-        default: out[i] = wgpt_pm::powf_(x[i], y[i]); break;
+        case 4: out[i] = wgpt_pm::powf_(x[i], y[i]); break;
+        // the device-only forms of the shading code, checked against the plain ones by the tests:
+        case 5: out[i] = (V3(x[i], -x[i], 0.0f) / y[i]).x; break;                    // shared-reciprocal vector division
+        case 6: { float sn, cs; wgpt_pm::sincosf_(x[i], &sn, &cs); out[i] = sn; break; }
+        default: { float sn, cs; wgpt_pm::sincosf_(x[i], &sn, &cs); out[i] = cs; break; }
     }
 }
 
