@@ -26,7 +26,9 @@ __device__ __forceinline__ v3 ray_color(const DeviceScene& S, Ray ray, uint32_t&
             prim.t = hit ? h.t : 0.0f;
         }
         if (!hit) { acc = acc + V3(0.0f, 1.0f, 1.0f) * throughput; break; }
-        finalize_hit(S, ray, h, oc, st);
+        TriNormals tn; tn.a = tn.b = tn.c = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (h.kind == HIT_TRI) tn = load_tri_normals(S, h.index);
+        finalize_hit(S, ray, h, tn, st);
         const Material m = S.materials[h.mat_id];
         unsigned draws = 0;
         bool early;

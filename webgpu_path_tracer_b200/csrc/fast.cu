@@ -154,7 +154,7 @@ static int ensure_pool(wgpt_ctx* c) {
     P.ctl = (WfControl*)carve(sizeof(WfControl));
     P.pool.e0 = (float4*)carve((size_t)cap * 16); P.pool.e1 = (float4*)carve((size_t)cap * 16);
     P.pool.s0 = (float4*)carve((size_t)cap * 16); P.pool.s1 = (float4*)carve((size_t)cap * 16);
-    P.pool.s2 = (float4*)carve((size_t)cap * 16); P.pool.pix = (float4*)carve((size_t)cap * 16);
+    P.pool.x = (float4*)carve((size_t)cap * 16);  P.pool.pix = (float4*)carve((size_t)cap * 16);
     P.pool.capacity = cap;
     P.q_extend = (uint32_t*)carve((size_t)cap * 4);
     P.stage = (float4*)carve((size_t)ring * npix * 16);

@@ -17,10 +17,19 @@ struct ShadeState {
     v3 unit_w, u, v;
 };
 
+// The three 16-byte records of a Triangle that hold its vertex normals (+ local_id, mesh_id in the
+// w lanes: header.wgsl:88-98, offsets 48 / 64 / 80), fetched ahead of the shading code.
+struct TriNormals { float4 a, b, c; };
+__device__ __forceinline__ TriNormals load_tri_normals(const DeviceScene& S, int index) {
+    const float4* tp = reinterpret_cast<const float4*>(&S.triangles[index]);
+    TriNormals t; t.a = __ldg(&tp[3]); t.b = __ldg(&tp[4]); t.c = __ldg(&tp[5]);
+    return t;
+}
+
 // What hit_sphere / hit_volume / hit_quad / hit_triangle store into hitRec on accept
 // (common.wgsl:54-71, 140-143, 176-185, 224-239), computed once for the closest hit.
 __device__ __forceinline__ void finalize_hit(const DeviceScene& S, const Ray& ray, const HitLite& h,
-                                             ObjRayCache& oc, ShadeState& st) {
+                                             const TriNormals& tn, ShadeState& st) {
     st.p = at(ray, h.t);
     if (h.kind == HIT_SPHERE) {
         const Sphere s = S.spheres[h.index];
@@ -36,10 +45,9 @@ __device__ __forceinline__ void finalize_hit(const DeviceScene& S, const Ray& ra
         st.front_face = dot(ray.d, st.n) < 0.0f;
         if (!st.front_face) st.n = -st.n;
     } else {
-        const Triangle* tri = &S.triangles[h.index];
         const float ww = fs(fs(1.0f, h.uu), h.vv);
-        const v3 nn = (ld3(tri->nA) * ww + ld3(tri->nB) * h.uu) + ld3(tri->nC) * h.vv;
-        const Mesh m = S.meshes[(int)tri->mesh_id];
+        const v3 nn = (V3(tn.a.x, tn.a.y, tn.a.z) * ww + V3(tn.b.x, tn.b.y, tn.b.z) * h.uu) + V3(tn.c.x, tn.c.y, tn.c.z) * h.vv;
+        const Mesh m = S.meshes[(int)tn.c.w];
         st.n = normalize(mulT4_xyz0(S.transforms[m.global_id].invModelMatrix, nn));
         st.front_face = dot(ray.d, st.n) < 0.0f;
         if (!st.front_face) st.n = -st.n;

@@ -33,7 +33,7 @@ __device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0,
 
 __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < P.pool.capacity) P.pool.e1[i] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_tag(HIT_NONE, WF_CLS_IDLE, -1)));
+    if (i < P.pool.capacity) P.pool.x[i] = make_float4(__uint_as_float(wf_tag(HIT_NONE, WF_CLS_IDLE, -1)), 0.0f, 0.0f, 0.0f);
     if (i == 0) {
         WfControl* c = P.ctl;
         c->next_work = 0;
@@ -121,9 +121,9 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     if (idx < n) {
                         slot = P.q_extend[idx];
                         const float4 o4 = P.pool.e0[slot], d4 = P.pool.e1[slot];
-                        tag0 = __float_as_uint(d4.w);
+                        tag0 = __float_as_uint(P.pool.x[slot].x);
                         ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
-                        // sphere/quad result carried in by shade; its index stays in the slot (s2.y), which
+                        // sphere/quad result carried in by shade; its index stays in the slot (x.y), which
                         // this stage only overwrites when a triangle wins
                         h.t = o4.w; h.uu = 0.0f; h.vv = 0.0f; h.kind = wf_tag_kind(tag0); h.index = -1; h.mat_id = wf_tag_mat(tag0);
                         hit_a = h.kind != HIT_NONE;
@@ -193,23 +193,23 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     // resolves it (inline, one such ray stalled the other 31 lanes of this warp for the length
                     // of a latency-bound binary walk; in shade the other warps of the SM hide that latency).
                     // A tie carries the closest distance along, an overflow of the wide stack does not.
-                    if (!ambiguous) reinterpret_cast<float*>(&P.pool.s2[slot])[2] = closest;
-                    reinterpret_cast<uint32_t*>(&P.pool.e1[slot])[3] = (tag0 & ~0xf0u) | ((uint32_t)(ambiguous ? WF_CLS_OVERFLOW : WF_CLS_TIE) << 4);
+                    if (!ambiguous) reinterpret_cast<float*>(&P.pool.x[slot])[2] = closest;
+                    reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = (tag0 & ~0xf0u) | ((uint32_t)(ambiguous ? WF_CLS_OVERFLOW : WF_CLS_TIE) << 4);
                 } else {
                     const bool hit = hit_a | hit_t;
                     const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
                     uint32_t tag = (tag0 & ~0xf0u) | ((uint32_t)cls << 4);          // the sphere/quad hit (or the miss) stands
                     if (hit_t) {
                         tag = wf_tag(HIT_TRI, cls, h.mat_id);
-                        float* e0 = reinterpret_cast<float*>(&P.pool.e0[slot]);
-                        float* s2 = reinterpret_cast<float*>(&P.pool.s2[slot]);
-                        e0[3] = h.t; s2[1] = __int_as_float(h.index); s2[2] = h.uu; s2[3] = h.vv;
+                        reinterpret_cast<float*>(&P.pool.e0[slot])[3] = h.t;
+                        P.pool.x[slot] = make_float4(__uint_as_float(tag), __int_as_float(h.index), h.uu, h.vv);
+                    } else {
+                        reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = tag;
                     }
-                    reinterpret_cast<uint32_t*>(&P.pool.e1[slot])[3] = tag;
                     if (P.prim_type) {
-                        const float4 s1v = P.pool.s1[slot], s2v = P.pool.s2[slot];
-                        if ((__float_as_uint(s2v.x) & 0x03ffffffu) == 0u) {                // first query of the item: the primary ray
-                            if (!hit_t) h.index = __float_as_int(s2v.y);
+                        const float4 e1v = P.pool.e1[slot], s1v = P.pool.s1[slot];
+                        if ((__float_as_uint(e1v.w) & 0x03ffffffu) == 0u) {                // first query of the item: the primary ray
+                            if (!hit_t) h.index = __float_as_int(P.pool.x[slot].y);
                             write_probe(S, P, __float_as_uint(s1v.w), hit, h);
                         }
                     }
@@ -271,7 +271,7 @@ template <bool COUNT>
 __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(DeviceScene S, WfParams P) {
     __shared__ uint32_t s_done[WF_MAX_RING];
     __shared__ uint32_t s_key_cnt[32];                 // slots per shade key
-    __shared__ float4 s_e1[WF_SHADE_THREADS];           // (ray direction, tag) of the block's slots
+    __shared__ float4 s_x[WF_SHADE_THREADS];            // (tag, hit index, u, v) of the block's slots
     __shared__ uint32_t s_perm[WF_SHADE_THREADS];
     __shared__ uint32_t s_q[WF_SHADE_THREADS];          // slot ids for the next ray queue
     __shared__ uint32_t s_qn, s_arrived;
@@ -289,10 +289,10 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     if (threadIdx.x < 32) s_key_cnt[threadIdx.x] = 0;
     {
         const uint32_t s0 = block_base + threadIdx.x;
-        float4 e1v = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(wf_tag(HIT_NONE, WF_CLS_DEAD, -1)));
-        if (s0 < P.pool.capacity) e1v = P.pool.e1[s0];
-        s_e1[threadIdx.x] = e1v;
-        const int cls0 = wf_tag_cls(__float_as_uint(e1v.w)), kind0 = wf_tag_kind(__float_as_uint(e1v.w));
+        float4 xv0 = make_float4(__uint_as_float(wf_tag(HIT_NONE, WF_CLS_DEAD, -1)), 0.0f, 0.0f, 0.0f);
+        if (s0 < P.pool.capacity) xv0 = P.pool.x[s0];
+        s_x[threadIdx.x] = xv0;
+        const int cls0 = wf_tag_cls(__float_as_uint(xv0.x)), kind0 = wf_tag_kind(__float_as_uint(xv0.x));
         const uint32_t key = cls0 < WF_CLS_MISS ? (uint32_t)(cls0 * 4 + (kind0 & 3)) : (uint32_t)(12 + cls0);
         const uint32_t peers = __match_any_sync(0xffffffffu, key);
         const int leader = __ffs((int)peers) - 1;
@@ -312,17 +312,29 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     }
     const uint32_t j = s_perm[threadIdx.x];
     const uint32_t slot = block_base + j;
-    const float4 e1v = s_e1[j];
+    const float4 xv = s_x[j];
     // (hit kind, hit index, material id, shade class) of the slot
-    int4 hid = make_int4(wf_tag_kind(__float_as_uint(e1v.w)), -1, wf_tag_mat(__float_as_uint(e1v.w)), wf_tag_cls(__float_as_uint(e1v.w)));
+    int4 hid = make_int4(wf_tag_kind(__float_as_uint(xv.x)), __float_as_int(xv.y), wf_tag_mat(__float_as_uint(xv.x)), wf_tag_cls(__float_as_uint(xv.x)));
     int cls = hid.w;
+    // The slot's records and -- the hit is known from the tag -- the triangle's normals are requested NOW,
+    // in one batch of independent loads, so that shading waits for one memory round trip instead of a
+    // chain of three.  (Also preloading the material and the pixel sum cost more in registers than the
+    // shorter chain gave back: measured.)
+    float4 e0v = make_float4(0.0f, 0.0f, 0.0f, 0.0f), e1v = e0v, s0v = e0v, s1v = e0v;
+    TriNormals tn; tn.a = tn.b = tn.c = e0v;
+    if (cls <= WF_CLS_MISS || cls >= WF_CLS_TIE) {
+        e0v = P.pool.e0[slot]; e1v = P.pool.e1[slot]; s0v = P.pool.s0[slot]; s1v = P.pool.s1[slot];
+        if (cls < WF_CLS_MISS) {
+            if (hid.x == HIT_TRI) tn = load_tri_normals(S, hid.y);
+        }
+    }
     float4 h4_resolved = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     bool resolved = false;
     if (cls >= WF_CLS_TIE) {
         // ---- tie resolver: closest hit in reference order (hitRay.wgsl:42-110) for the rays extend marked ----
-        const float4 o4 = P.pool.e0[slot], s2v = P.pool.s2[slot];
+        const float4 o4 = e0v;
         Ray r; r.o = V3(o4.x, o4.y, o4.z); r.d = V3(e1v.x, e1v.y, e1v.z);
-        HitLite h; h.t = o4.w; h.uu = 0.0f; h.vv = 0.0f; h.kind = hid.x; h.index = __float_as_int(s2v.y); h.mat_id = hid.z;
+        HitLite h; h.t = o4.w; h.uu = 0.0f; h.vv = 0.0f; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
         const bool hit_a = hid.x != HIT_NONE;
         float closest = hit_a ? o4.w : WGPT_MAX_FLOAT;
         ObjRayCache oc; oc.reset();
@@ -331,15 +343,18 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         // visits, so the walk only needs the nodes overlapping [D(1 - 1e-4), closest].  (Not when the
         // reference's stack guard could fire: its abort depends on everything visited.)
         const bool restricted = cls == WF_CLS_TIE && P.bvh_depth < S.K.STACK_SIZE && P.bvh_depth < WGPT_MAX_STACK;
-        const float box_tmin = restricted ? fmaxf(WGPT_RAY_TMIN, s2v.z * 0.9999f) : WGPT_RAY_TMIN;
+        const float box_tmin = restricted ? fmaxf(WGPT_RAY_TMIN, xv.z * 0.9999f) : WGPT_RAY_TMIN;
         const bool hit = hit_bvh_binary(S, r, nullptr, oc, closest, h, box_tmin) | hit_a;
         cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
         hid = make_int4(hit ? h.kind : (int)HIT_NONE, h.index, h.mat_id, cls);
         h4_resolved = make_float4(h.t, h.uu, h.vv, 1.0f);
         resolved = true;
+        if (hit) {                                              // the batch above was fetched for the unresolved hit
+            if (hid.x == HIT_TRI) tn = load_tri_normals(S, hid.y);
+        }
         atomicAdd(&ctl->fallbacks, 1u);
         if (P.prim_type) {
-            if ((__float_as_uint(s2v.x) & 0x03ffffffu) == 0u) write_probe(S, P, __float_as_uint(P.pool.s1[slot].w), hit, h);
+            if ((__float_as_uint(e1v.w) & 0x03ffffffu) == 0u) write_probe(S, P, __float_as_uint(s1v.w), hit, h);
         }
     }
 
@@ -359,8 +374,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         need_work = true;
     } else if (cls <= WF_CLS_MISS) {
         bool ended = false;
-        const float4 s0v = P.pool.s0[slot], s1v = P.pool.s1[slot], s2v = P.pool.s2[slot];
-        const uint32_t ctr = __float_as_uint(s2v.x);
+        const uint32_t ctr = __float_as_uint(e1v.w);
         rng = __float_as_uint(s1v.z); pix_i = __float_as_uint(s1v.w);
         ring_slot = ctr >> 26; bounce = (ctr >> 16) & 0x3ffu; scnt = ctr & 0xffffu;
         thr = V3(s0v.x, s0v.y, s0v.z); acc = V3(s0v.w, s1v.x, s1v.y);
@@ -368,16 +382,16 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
             acc = acc + V3(0.0f, 1.0f, 1.0f) * thr;
             ended = true;
         } else {
-            const float4 o4 = P.pool.e0[slot];
+            const float4 o4 = e0v;
             ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(e1v.x, e1v.y, e1v.z);
-            HitLite h; h.t = o4.w; h.uu = s2v.z; h.vv = s2v.w; h.kind = hid.x; h.index = __float_as_int(s2v.y); h.mat_id = hid.z;
+            HitLite h; h.t = o4.w; h.uu = xv.z; h.vv = xv.w; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
             if (resolved) { h.t = h4_resolved.x; h.uu = h4_resolved.y; h.vv = h4_resolved.z; h.index = hid.y; }
             ObjRayCache oc; oc.reset();
             ShadeState st;
             st.p = st.n = st.unit_w = st.u = st.v = V3s(0.0f);
             st.front_face = false; st.skip_pdf = false; st.doSpecular = 0.0f;
             st.skip_ray.o = st.skip_ray.d = V3s(0.0f);
-            finalize_hit(S, ray, h, oc, st);
+            finalize_hit(S, ray, h, tn, st);
             const Material m = S.materials[h.mat_id];
             bool early;
             const bool cont = bounce_update(S, m, (int)bounce, ray, st, rng, n_draws, acc, thr, early);
@@ -470,14 +484,14 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         const int ncls = trace ? WF_CLS_TRACE : (hit_a ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS);
         const uint32_t ctr = wf_ctr(ring_slot, bounce, scnt);
         P.pool.e0[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, h.t);
-        P.pool.e1[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(wf_tag(hit_a ? h.kind : (int)HIT_NONE, ncls, h.mat_id)));
+        P.pool.e1[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(ctr));
         P.pool.s0[slot] = make_float4(thr.x, thr.y, thr.z, acc.x);
         P.pool.s1[slot] = make_float4(acc.y, acc.z, __uint_as_float(rng), __uint_as_float(pix_i));
-        P.pool.s2[slot] = make_float4(__uint_as_float(ctr), __int_as_float(h.index), 0.0f, 0.0f);
+        P.pool.x[slot] = make_float4(__uint_as_float(wf_tag(hit_a ? h.kind : (int)HIT_NONE, ncls, h.mat_id)), __int_as_float(h.index), 0.0f, 0.0f);
         if (store_pix) P.pool.pix[slot] = pix;
         if (!trace && P.prim_type && (ctr & 0x03ffffffu) == 0u) write_probe(S, P, pix_i, hit_a, h);
     } else if (cls <= WF_CLS_IDLE && new_cls != cls) {
-        reinterpret_cast<uint32_t*>(&P.pool.e1[slot])[3] = wf_tag(HIT_NONE, new_cls, -1);    // idle (waiting for the window) or dead (no work left)
+        reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = wf_tag(HIT_NONE, new_cls, -1);    // idle (waiting for the window) or dead (no work left)
     }
 
     // ---- compact: rays that need the BVH into the next ray queue, one global atomic per block ----

@@ -26,15 +26,17 @@ namespace wg {
 // + the 16-byte pixel sum that is only touched when a sample starts or ends.  The shade stage is
 // HBM-bound on exactly these bytes (it reads and rewrites every live slot once per bounce), so
 // the state is packed: no padding lanes, ids in one word.
-//   e0 = (ray origin.xyz, hit t)                      written by shade (t of the sphere/quad hit) and extend (final t)
-//   e1 = (ray direction.xyz, tag)                      tag = (material id << 8) | (shade class << 4) | (hit kind + 1)
+//   x  = (tag, hit index, hit u, hit v)               tag = (material id << 8) | (shade class << 4) | (hit kind + 1);
+//        the record the shade stage reads FIRST: it holds the sort key and everything needed to address
+//        the hit's data (triangle normals, material), so all further loads can be issued at once.
+//        For WF_CLS_TIE the u lane carries the closest distance the extend stage found.
+//   e0 = (ray origin.xyz, hit t)
+//   e1 = (ray direction.xyz, counters)                 counters = (ring slot << 26) | (bounce << 16) | sample
 //   s0 = (throughput.xyz, radiance.x)
 //   s1 = (radiance.y, radiance.z, rng state, shard-local pixel)
-//   s2 = (counters, hit index, hit u, hit v)           counters = (ring slot << 26) | (bounce << 16) | sample
-//        For WF_CLS_TIE the u lane carries the closest distance the extend stage found.
-// The extend stage reads e0, e1 (32 B) and writes e0, e1 and the .yzw lanes of s2.
+// The extend stage reads e0, e1 and x.tag and writes x (and the t lane of e0) when a triangle wins.
 struct PathPool {
-    float4* e0; float4* e1; float4* s0; float4* s1; float4* s2;
+    float4* x; float4* e0; float4* e1; float4* s0; float4* s1;
     float4* pix;     // pixColor of the (pixel, frame) so far .xyz, .w = samples taken (stratified divisor)
     uint32_t capacity;
 };
