@@ -171,3 +171,21 @@ def test_renderer_mirror_saves_the_presented_image(default_scene, tmp_path):
     o.write_uniforms(1, 0, cam.viewMatrix)
     o.render(1, 4)
     assert np.array_equal(bits(o.read_framebuffer()), bits(r.webGPU.read_framebuffer()))
+
+
+@pytest.mark.parametrize("cfg", ["C2", "C4"])
+def test_full_size_primary_hits_and_radiance_fast_equals_exact(cfg):
+    """BASELINE.json's bar at the benchmark's own size: closest-hit primitive ids of every primary ray of the
+    1920x1080 frame bit-exact, and the per-sample radiance of the frame too (the fast path -- device-built
+    hierarchy, wide traversal, wavefront scheduling -- against the exact-mode kernel that walks the
+    reference's tree in the reference's order, itself pinned to the oracle at small sizes)."""
+    import bench_scenes
+    scene, cam, W, H, kw = bench_scenes.build(cfg)
+    e = setup(PathTracer(W, H, mode=MODE_EXACT, **kw), scene, cam, frame=3)
+    g = setup(PathTracer(W, H, mode=MODE_FAST, **kw), scene, cam, frame=3)
+    re_, te, ie, de = e.probe()
+    rg, tg, ig, dg = g.probe()
+    assert int((te != tg).sum()) == 0 and int((ie != ig).sum()) == 0
+    assert np.array_equal(bits(de), bits(dg))
+    assert np.array_equal(bits(re_), bits(rg))
+    assert (tg == 2).sum() > 10000          # the mesh is really in view
