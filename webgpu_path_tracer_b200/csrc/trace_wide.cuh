@@ -87,7 +87,7 @@ __device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nod
     const uint32_t nz[2] = {pz ? n3.x : n4.z, pz ? n3.y : n4.w}, fz[2] = {pz ? n4.z : n3.x, pz ? n4.w : n3.y};
     const float far_cap = closest * 1.000002f;
     // Straight-line code for all 8 slots (no divergence inside a node).  The sign of
-    // min(thi, far) - tlo is the MISS flag; a funnel shift collects the flags, slot 7 first, so
+    // the three differences below is the MISS flag; a funnel shift collects the flags, slot 7 first, so
     // slot s ends up in bit s.
     uint32_t miss = 0;
     #pragma unroll
@@ -100,10 +100,14 @@ __device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nod
         cvt2(nz[w], sel, tlz[0], tlz[1]); cvt2(fz[w], sel, thz[0], thz[1]);
         #pragma unroll
         for (int k = 1; k >= 0; k--) {
-            const float tlo = fmaxf(fmaxf(fmaf(tlx[k], adjx, ox), fmaf(tly[k], adjy, oy)), fmaxf(fmaf(tlz[k], adjz, oz), 0.0f));
-            const float thi = fminf(fminf(fmaf(thx[k], adjx, ox), fmaf(thy[k], adjy, oy)), fmaf(thz[k], adjz, oz)) * 1.000002f;
-            const float d = fminf(thi, far_cap) - tlo;               // d < 0 (or -0): miss
-            miss = __funnelshift_l(__float_as_uint(d), miss, 1);
+            // hit <=> tlo3 <= thi3 * (1 + 2^-19)  and  tlo3 <= far  and  thi3 >= 0  (the box is not behind the
+            // origin); each test is the sign of one FMA-pipe result, OR-ed in a single LOP3
+            const float tlo3 = fmaxf(fmaxf(fmaf(tlx[k], adjx, ox), fmaf(tly[k], adjy, oy)), fmaf(tlz[k], adjz, oz));
+            const float thi3 = fminf(fminf(fmaf(thx[k], adjx, ox), fmaf(thy[k], adjy, oy)), fmaf(thz[k], adjz, oz));
+            const float d1 = fmaf(thi3, 1.000002f, -tlo3);
+            const float d2 = far_cap - tlo3;
+            const uint32_t d = __float_as_uint(d1) | __float_as_uint(d2) | __float_as_uint(thi3);
+            miss = __funnelshift_l(d, miss, 1);
         }
     }
     return ~miss & (imask | lmask);
