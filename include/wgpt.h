@@ -149,6 +149,19 @@ int wgpt_stage_timings(wgpt_ctx* ctx, float ms[4], uint64_t launches[4]);
  * one-reduction sincos (device-only forms that must equal the plain ones bit for bit) */
 int wgpt_pinned_math(wgpt_ctx* ctx, int fn, int n, const float* x, const float* y, float* out);
 
+/* K4 stream timing for the roofline of the accumulate / present passes ("a pure
+ * stream"): runs `reps` launches of kernel 0 = accumulate (16 B read staging + 16 B read + 16 B
+ * write of binding 3 per pixel), 1 = present to RGBA8 (16 B read + 4 B write), 2 = present to f32
+ * RGBA (16 B + 16 B) on device scratch of the context's image size, WITHOUT touching binding 3, and
+ * returns the mean device time per launch (CUDA events) and the bytes one launch moves. */
+int wgpt_k4_timing(wgpt_ctx* ctx, int kernel, int reps, float* ms_per_launch, uint64_t* bytes_per_launch);
+
+/* The bytes-only present (rgba_out == NULL) decides round(255 pow(c, 1/2.2)) from an SFU estimate
+ * when that is provably enough and from the pinned pow otherwise.  This hook compares the two for
+ * every float whose bit pattern lies in [first_bits, first_bits + count) ON THE GPU and returns the
+ * number of differing bytes (must be 0) and how many inputs took the pinned path. */
+int wgpt_present_quant_check(wgpt_ctx* ctx, uint32_t first_bits, uint32_t count, uint64_t* mismatches, uint64_t* exact_path);
+
 #ifdef __cplusplus
 }
 #endif

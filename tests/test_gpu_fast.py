@@ -173,6 +173,32 @@ def test_renderer_mirror_saves_the_presented_image(default_scene, tmp_path):
     assert np.array_equal(bits(o.read_framebuffer()), bits(r.webGPU.read_framebuffer()))
 
 
+def test_bytes_only_present_equals_the_pinned_pow_for_every_float(default_scene):
+    """K4 present to the 8-bit canvas skips the binary64 pow when an SFU estimate already decides the byte.
+    Exhaustive proof: round(255 pow(r, 1/2.2)) agrees with the pinned pow for EVERY float r in [0, 1] (the
+    tone map clamps to that range), for -0, and for NaN / out-of-range patterns (which take the pinned path);
+    and on a rendered image the bytes-only present equals the bytes of the float present."""
+    scene, cam = default_scene
+    g = setup(PathTracer(96, 64, mode=MODE_FAST), scene, cam)
+    bad, slow = g.present_quant_check(0, 0x3f800000 + 1)
+    assert bad == 0
+    assert slow < 0.01 * 0x3f800000          # the pinned path is the exception
+    for first, count in ((0x3f800001, 1 << 16), (0x7f800000, 1 << 16), (0x80000000, 1 << 16), (0xffc00000, 16)):
+        assert g.present_quant_check(first, count)[0] == 0
+    g.render(1, 5)
+    g.write_uniforms(5, 0, cam.viewMatrix)
+    both = g.present(rgba8=True)[1]
+    only = g.present(rgba8="only")
+    assert np.array_equal(both, only)
+    o = Oracle(96, 64)
+    o.write_scene(scene.buffers())
+    o.write_uniforms(1, 0, cam.viewMatrix)
+    o.render(1, 5)
+    o.write_uniforms(5, 0, cam.viewMatrix)
+    img = np.asarray(o.present()).reshape(-1, 4)
+    assert np.array_equal(only[:, :3], np.rint(img[:, :3] * np.float32(255.0)).astype(np.uint8))
+
+
 @pytest.mark.parametrize("cfg", ["C2", "C4"])
 def test_full_size_primary_hits_and_radiance_fast_equals_exact(cfg):
     """BASELINE.json's bar at the benchmark's own size: closest-hit primitive ids of every primary ray of the

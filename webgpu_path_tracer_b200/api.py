@@ -19,7 +19,7 @@ COUNTER_NAMES = ("rays", "node_visits", "tri_tests", "sphere_tests", "quad_tests
 EXPORTS = ("wgpt_default_config", "wgpt_create", "wgpt_destroy", "wgpt_last_error", "wgpt_write_buffer",
            "wgpt_read_buffer", "wgpt_device_ptr", "wgpt_dispatch", "wgpt_render", "wgpt_present", "wgpt_probe",
            "wgpt_trace_rays", "wgpt_counters", "wgpt_set_counters", "wgpt_last_timing", "wgpt_synchronize",
-           "wgpt_pinned_math", "wgpt_fast_statistics", "wgpt_set_stage_profiling", "wgpt_stage_timings")
+           "wgpt_pinned_math", "wgpt_fast_statistics", "wgpt_set_stage_profiling", "wgpt_stage_timings", "wgpt_k4_timing", "wgpt_present_quant_check")
 
 
 class WgptError(RuntimeError):
@@ -77,6 +77,8 @@ def load_library(path=None):
     L.wgpt_last_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_uint64)]
     L.wgpt_synchronize.argtypes = [vp]
     L.wgpt_pinned_math.argtypes = [vp, i32, i32, vp, vp, vp]
+    L.wgpt_k4_timing.argtypes = [vp, i32, i32, vp, vp]
+    L.wgpt_present_quant_check.argtypes = [vp, u32, u32, vp, vp]
     L.wgpt_fast_statistics.argtypes = [vp, C.POINTER(FastStats)]
     L.wgpt_set_stage_profiling.argtypes = [vp, i32]
     L.wgpt_stage_timings.argtypes = [vp, C.POINTER(C.c_float * 4), C.POINTER(C.c_uint64 * 4)]
@@ -162,9 +164,12 @@ class PathTracer:
         self._ck(self.L.wgpt_render(self.h, int(first_frame), int(n_frames)), "wgpt_render")
 
     def present(self, rgba8=False):
-        out = np.empty((self.H * self.W, 4), np.float32)
+        """fs output as float RGBA; rgba8=True adds the 8-bit canvas bytes; rgba8="only" returns just the bytes."""
+        out = np.empty((self.H * self.W, 4), np.float32) if rgba8 != "only" else None
         out8 = np.empty((self.H * self.W, 4), np.uint8) if rgba8 else None
         self._ck(self.L.wgpt_present(self.h, _p(out), _p(out8)), "wgpt_present")
+        if rgba8 == "only":
+            return out8
         return (out, out8) if rgba8 else out
 
     def synchronize(self):
@@ -212,6 +217,19 @@ class PathTracer:
         self._ck(self.L.wgpt_stage_timings(self.h, C.byref(ms), C.byref(n)), "wgpt_stage_timings")
         names = ("extend", "shade", "control_accumulate", "wide_build")
         return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(names)}
+
+    def k4_timing(self, kernel, reps=20):
+        """Mean device ms and bytes of one K4 launch: kernel = 'accumulate' | 'present_rgba8' | 'present_f32'."""
+        names = {"accumulate": 0, "present_rgba8": 1, "present_f32": 2}
+        ms, nbytes = C.c_float(), C.c_uint64()
+        self._ck(self.L.wgpt_k4_timing(self.h, names[kernel], int(reps), C.byref(ms), C.byref(nbytes)), "wgpt_k4_timing")
+        return float(ms.value), int(nbytes.value)
+
+    def present_quant_check(self, first_bits, count):
+        """(mismatching bytes, inputs on the pinned path) of the bytes-only present over a range of float bit patterns."""
+        bad, slow = C.c_uint64(), C.c_uint64()
+        self._ck(self.L.wgpt_present_quant_check(self.h, int(first_bits), int(count), C.byref(bad), C.byref(slow)), "wgpt_present_quant_check")
+        return int(bad.value), int(slow.value)
 
     def pinned_math(self, fn, x, y=None):
         names = {"sin": 0, "cos": 1, "acos": 2, "log": 3, "pow": 4, "vdiv": 5, "sincos_sin": 6, "sincos_cos": 7}

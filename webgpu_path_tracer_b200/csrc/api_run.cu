@@ -1,5 +1,6 @@
 // api_run.cu -- the per-frame half of the C ABI: dispatch / render / present and the parity hooks.
 // Mirrors /root/reference/renderer.js:163-191 and webgpu-utils.js:125-148.
+#include <vector>
 #include <string.h>
 #include "context.h"
 #include "kernels.cuh"
@@ -247,6 +248,59 @@ int wgpt_pinned_math(wgpt_ctx* c, int fn, int n, const float* x, const float* y,
     launch_pinned_math(fn, n, (const float*)dx.p, (const float*)dy.p, (float*)dout.p, c->stream);
     cudaMemcpyAsync(out, dout.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream);
     return cuda_err(c, cudaStreamSynchronize(c->stream), "pinned_math");
+}
+
+int wgpt_k4_timing(wgpt_ctx* c, int kernel, int reps, float* ms_per_launch, uint64_t* bytes_per_launch) {
+    if (!c || kernel < 0 || kernel > 2 || reps < 1 || !ms_per_launch) return WGPT_E_INVALID;
+    cudaSetDevice(c->cfg.device);
+    const uint32_t npix = (uint32_t)c->cfg.width * c->cfg.height;
+    HostScratch d_fb, d_frame, d_out;
+    cudaError_t e;
+    if ((e = cudaMalloc(&d_fb.p, (size_t)npix * 16)) != cudaSuccess || (e = cudaMalloc(&d_frame.p, (size_t)npix * 16)) != cudaSuccess ||
+        (e = cudaMalloc(&d_out.p, (size_t)npix * 16)) != cudaSuccess) return cuda_err(c, e, "k4_timing");
+    cudaMemsetAsync(d_fb.p, 0, (size_t)npix * 16, c->stream);
+    {   // a frame of varied radiance sums (LCG, 0 .. 16 x frameNum), w = 1: every pixel is "rendered"
+        std::vector<float> h((size_t)npix * 4);
+        uint32_t x = 12345u;
+        for (size_t i = 0; i < h.size(); i++) { x = x * 1664525u + 1013904223u; h[i] = (i & 3) == 3 ? 1.0f : (float)(x >> 8) * (112.0f / 16777216.0f); }
+        cudaMemcpyAsync(d_frame.p, h.data(), h.size() * 4, cudaMemcpyHostToDevice, c->stream);
+        cudaStreamSynchronize(c->stream);
+    }
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    for (int pass = 0; pass < 2; pass++) {                                   // pass 0 = warm-up
+        if (pass) cudaEventRecord(a, c->stream);
+        for (int r = 0; r < (pass ? reps : 3); r++) {
+            if (kernel == 0) launch_accumulate((float4*)d_fb.p, (const float4*)d_frame.p, npix, 0, c->stream);
+            else launch_present((const float4*)d_frame.p, nullptr, kernel == 2 ? (float4*)d_out.p : nullptr,
+                                kernel == 1 ? (uchar4*)d_out.p : nullptr, npix, 7.0f, 0, c->stream);
+        }
+        if (pass) cudaEventRecord(b, c->stream);
+    }
+    e = cudaStreamSynchronize(c->stream);
+    float t = 0.0f;
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&t, a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    if (e != cudaSuccess) return cuda_err(c, e, "k4_timing");
+    *ms_per_launch = t / (float)reps;
+    if (bytes_per_launch) *bytes_per_launch = (uint64_t)npix * (kernel == 0 ? 48u : kernel == 1 ? 20u : 32u);
+    return WGPT_OK;
+}
+
+int wgpt_present_quant_check(wgpt_ctx* c, uint32_t first_bits, uint32_t count, uint64_t* mismatches, uint64_t* exact_path) {
+    if (!c || !mismatches) return WGPT_E_INVALID;
+    cudaSetDevice(c->cfg.device);
+    HostScratch d;
+    cudaError_t e = cudaMalloc(&d.p, 16);
+    if (e != cudaSuccess) return cuda_err(c, e, "present_quant_check");
+    cudaMemsetAsync(d.p, 0, 16, c->stream);
+    launch_quant_check(first_bits, count, (unsigned long long*)d.p, c->stream);
+    unsigned long long h[2] = {0, 0};
+    cudaMemcpyAsync(h, d.p, 16, cudaMemcpyDeviceToHost, c->stream);
+    if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) return cuda_err(c, e, "present_quant_check");
+    *mismatches = h[0];
+    if (exact_path) *exact_path = h[1];
+    return WGPT_OK;
 }
 
 }  // extern "C"

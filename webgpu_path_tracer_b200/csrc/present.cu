@@ -20,21 +20,80 @@ __device__ __forceinline__ float tonemap1(float sum, float frameNum) {
     return wgpt_pm::powf_(r, 0.45454545454545453f);
 }
 
+// aces + clamp part of tonemap1 (exact float; NaN stays NaN through pmin/pmax like the oracle's)
+template <bool BYTES_ONLY>
+__device__ __forceinline__ float tonemap_pre(float sum, float frameNum, float rcp_frame, bool frame_ok) {
+    const float col = fdiv_shared(sum, frameNum, rcp_frame, frame_ok);      // == fd(sum, frameNum), one reciprocal per kernel
+    const float v1 = fm(col, 0.6f);
+    const float r = fd(fm(v1, fa(fm(2.51f, v1), 0.03f)), fa(fm(v1, fa(fm(2.43f, v1), 0.59f)), 0.14f));
+    // the sign of a zero cannot reach a byte (pow(+-0) = 0), so the bytes-only pass uses the bare FMNMX
+    if (BYTES_ONLY) return fminf(fmaxf(r, 0.0f), 1.0f);
+    return pmin(pmax(r, 0.0f), 1.0f);
+}
+__device__ __forceinline__ unsigned char quant8_exact(float r) {
+    return (unsigned char)__float2uint_rn(wgpt_pm::powf_(r, 0.45454545454545453f) * 255.0f);
+}
+// round(255 * pow(r, 1/2.2)) for the 8-bit canvas WITHOUT the binary64 pow whenever the answer is
+// already decided: p~ = ex2(lg2(r) / 2.2) on the SFU has relative error < (2.5 + |t| / 2) 2^-22
+// (lg2.approx: 2^-22 absolute on the mantissa part; ex2.approx: 2 ulp), so if 255 p~ is further than
+// that from a rounding boundary k + 1/2 the rounded byte equals the pinned one.  Otherwise (about 3
+// pixels in 10^4) the pinned pow decides.  The test suite checks the byte against quant8_exact for
+// EVERY float in [0, 1] (wgpt_present_quant_check), so the bound is verified, not trusted.
+__device__ __forceinline__ unsigned char quant8(float r, unsigned* slow) {
+    float l, p;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(r));
+    const float t = l * 0.45454545454545453f;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p) : "f"(t));
+    const float v = p * 255.0f;
+    const float m = v + 12582912.0f;                       // 1.5 * 2^23: the sum's low mantissa bits are rint(v), no F2I
+    const float k = m - 12582912.0f;
+    const float err = fmaf(v * (2.5f + 0.5f * fabsf(t)), 2.3841858e-07f, 1.0e-7f);
+    // decided <=> v is at least err away from both k - 1/2 and k + 1/2 (false for NaN, which takes the pinned path)
+    if (0.5f - fabsf(v - k) > err) return (unsigned char)(__float_as_uint(m) & 0xffu);
+    if (slow) (*slow)++;
+    return quant8_exact(r);
+}
+
 __global__ void __launch_bounds__(256) k_present(const float4* __restrict__ fb_in, float4* __restrict__ fb_clear,
                                                  float4* __restrict__ rgba_out, uchar4* __restrict__ rgba8_out,
                                                  uint32_t npix, float frameNum, int clear) {
+    const bool frame_ok = frameNum > 8.67e-19f && frameNum < 1.15e18f;
+    float r0;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(frameNum));
+    const float rcp_frame = __fmaf_rn(r0, __fmaf_rn(-frameNum, r0, 1.0f), r0);
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
         const float4 s = fb_in[i];
-        float4 c;
-        c.x = tonemap1(s.x, frameNum); c.y = tonemap1(s.y, frameNum); c.z = tonemap1(s.z, frameNum); c.w = 1.0f;
-        if (rgba_out) rgba_out[i] = c;
-        if (rgba8_out) {
-            // canvas quantisation: round(c * 255); NaN (0/0 before the first frame) maps to 0
-            rgba8_out[i] = make_uchar4((unsigned char)__float2uint_rn(c.x * 255.0f), (unsigned char)__float2uint_rn(c.y * 255.0f),
-                                       (unsigned char)__float2uint_rn(c.z * 255.0f), 255);
+        if (rgba_out) {
+            float4 c;
+            c.x = tonemap1(s.x, frameNum); c.y = tonemap1(s.y, frameNum); c.z = tonemap1(s.z, frameNum); c.w = 1.0f;
+            rgba_out[i] = c;
+            if (rgba8_out) {
+                // canvas quantisation: round(c * 255); NaN (0/0 before the first frame) maps to 0
+                rgba8_out[i] = make_uchar4((unsigned char)__float2uint_rn(c.x * 255.0f), (unsigned char)__float2uint_rn(c.y * 255.0f),
+                                           (unsigned char)__float2uint_rn(c.z * 255.0f), 255);
+            }
+        } else if (rgba8_out) {
+            // bytes only (what the reference's 8-bit canvas shows): 16 B in, 4 B out, no binary64 in the common case
+            rgba8_out[i] = make_uchar4(quant8(tonemap_pre<true>(s.x, frameNum, rcp_frame, frame_ok), nullptr),
+                                       quant8(tonemap_pre<true>(s.y, frameNum, rcp_frame, frame_ok), nullptr),
+                                       quant8(tonemap_pre<true>(s.z, frameNum, rcp_frame, frame_ok), nullptr), 255);
         }
         if (clear) fb_clear[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
+}
+
+// every float r with bit pattern in [first, first + n): does quant8(r) equal quant8_exact(r)?
+__global__ void __launch_bounds__(256) k_quant_check(uint32_t first, uint32_t n, unsigned long long* __restrict__ out) {
+    unsigned bad = 0, slow = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float r = __uint_as_float(first + i);
+        if (quant8(r, &slow) != quant8_exact(r)) bad++;
+    }
+    for (int o = 16; o > 0; o >>= 1) { bad += __shfl_down_sync(0xffffffffu, bad, o); slow += __shfl_down_sync(0xffffffffu, slow, o); }
+    if ((threadIdx.x & 31) == 0) { if (bad) atomicAdd(&out[0], (unsigned long long)bad); if (slow) atomicAdd(&out[1], (unsigned long long)slow); }
+}
+void launch_quant_check(uint32_t first, uint32_t n, unsigned long long* out, cudaStream_t stream) {
+    if (n) k_quant_check<<<148 * 8, 256, 0, stream>>>(first, n, out);
 }
 
 __global__ void __launch_bounds__(256) k_accumulate(float4* __restrict__ fb, const float4* __restrict__ frame,

@@ -78,6 +78,6 @@ class Renderer:
 
     def save_image(self, path):
         """Write what the canvas would show (fs output, RGBA8) to a .png or .ppm file."""
-        rgba8 = np.asarray(self.present(rgba8=True)[1]).reshape(self.HEIGHT, self.WIDTH, 4)
+        rgba8 = np.asarray(self.present(rgba8="only")).reshape(self.HEIGHT, self.WIDTH, 4)
         (imageio.write_ppm if str(path).lower().endswith(".ppm") else imageio.write_png)(path, rgba8)
         return rgba8
