@@ -26,7 +26,7 @@
 namespace wg {
 
 #ifndef WF_REFILL_BELOW
-#define WF_REFILL_BELOW 26      // refill the warp when fewer lanes than this still traverse
+#define WF_REFILL_BELOW 22      // refill the warp when fewer lanes than this still traverse (finished lanes write back together then)
 #endif
 
 __device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
@@ -72,9 +72,13 @@ __device__ __forceinline__ bool root_box_hit(const DeviceScene& S, const Ray& ra
 // The sphere/quad part of hitScene (hitRay.wgsl:6-40) was already evaluated by the shade stage
 // when it produced the ray (all lanes in lock step there); this kernel walks the wide BVH.
 // Node visits and triangle tests run as separate warp phases: a lane that found candidate
-// triangles parks them until TRI_BATCH lanes have some (or nobody has node work left).
+// triangles parks them and goes on with its next node; the triangle phase runs once TRI_BATCH
+// lanes have parked triangles
 #ifndef WF_TRI_BATCH
-#define WF_TRI_BATCH 8
+#define WF_TRI_BATCH 16
+#endif
+#ifndef WF_TRI_ADAPT
+#define WF_TRI_ADAPT 2       // ... or as soon as ADAPT x (lanes with parked triangles) >= lanes with node work: measured sweep, DESIGN.md 4
 #endif
 
 #ifndef WF_EXTEND_MINB
@@ -103,10 +107,45 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
     uint2 G = make_uint2(0u, 0u);
     uint32_t tm = 0, tri_base = 0, tri_lmask = 0;   // parked candidate triangles of the last node visited: hit leaf slots, first
                                                     // packed triangle, leaf-slot mask (triangle of slot b = tri_base + popc(lmask below b))
+    // A second, PARKED set of candidate triangles: a lane whose node visit found leaf hits parks them and goes
+    // on with its next node instead of idling until enough lanes have triangles for a triangle phase; it only
+    // blocks when a later visit finds leaf hits while the parked set is still waiting.
+    uint32_t pk = 0, ptri_base = 0;                 // parked: hit leaf slots (bits 0-7) | leaf-slot mask << 8; first packed triangle
     uint2 stack[WIDE_STACK];
     int sp = 0;
 
     while (true) {
+        // ---- lanes whose walk is over write their result back and free the lane ----
+        if (has && tm == 0u && (pk & 0xffu) == 0u && !(G.y & 0xff000000u) && sp == 0) {
+            if (ambiguous | tie) {
+                // equal-distance triangles or a stack overflow: the reference-order walk decides.  The slot
+                // still holds the ray and its sphere/quad result; it is only MARKED here and the shade stage
+                // resolves it (inline, one such ray stalled the other 31 lanes of this warp for the length
+                // of a latency-bound binary walk; in shade the other warps of the SM hide that latency).
+                // A tie carries the closest distance along, an overflow of the wide stack does not.
+                if (!ambiguous) reinterpret_cast<float*>(&P.pool.x[slot])[2] = closest;
+                reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = (tag0 & ~0xf0u) | ((uint32_t)(ambiguous ? WF_CLS_OVERFLOW : WF_CLS_TIE) << 4);
+            } else {
+                const bool hit = hit_a | hit_t;
+                const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
+                uint32_t tag = (tag0 & ~0xf0u) | ((uint32_t)cls << 4);          // the sphere/quad hit (or the miss) stands
+                if (hit_t) {
+                    tag = wf_tag(HIT_TRI, cls, h.mat_id);
+                    reinterpret_cast<float*>(&P.pool.e0[slot])[3] = h.t;
+                    P.pool.x[slot] = make_float4(__uint_as_float(tag), __int_as_float(h.index), h.uu, h.vv);
+                } else {
+                    reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = tag;
+                }
+                if (P.prim_type) {
+                    const float4 e1v = P.pool.e1[slot], s1v = P.pool.s1[slot];
+                    if ((__float_as_uint(e1v.w) & 0x03ffffffu) == 0u) {                // first query of the item: the primary ray
+                        if (!hit_t) h.index = __float_as_int(P.pool.x[slot].y);
+                        write_probe(S, P, __float_as_uint(s1v.w), hit, h);
+                    }
+                }
+            }
+            has = false;
+        }
         // ---- dynamic ray fetch: every lane without a ray takes the next queue entry ----
         if (!exhausted) {
             const uint32_t m = __ballot_sync(0xffffffffu, !has);
@@ -129,7 +168,7 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                         hit_a = h.kind != HIT_NONE;
                         closest = hit_a ? o4.w : WGPT_MAX_FLOAT;
                         oc.reset();
-                        hit_t = false; ambiguous = false; tie = false; sp = 0; tm = 0;
+                        hit_t = false; ambiguous = false; tie = false; sp = 0; tm = 0; pk = 0;
                         wr = make_wide_ray(ray);
                         G = make_uint2(0u, 0x80000000u);
                         has = true;
@@ -153,7 +192,7 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     if (sp >= WIDE_STACK) overflow = true;          // deeper than the wide stack: reference walk decides
                     else stack[sp++] = G;
                 }
-                if (overflow) { ambiguous = true; G.y = 0u; sp = 0; }
+                if (overflow) { ambiguous = true; G.y = 0u; sp = 0; pk = 0u; }
                 else {
                     const uint32_t sl = (bit - 24u) ^ wr.octinv;
                     const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << sl) & 0xffu);
@@ -162,16 +201,18 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     const uint32_t hits = wide_node_hits(WB.nodes, G.x + rel, ray, wr, closest, child_base, tri_base, imask, lmask);
                     G = make_uint2(child_base, ((uint32_t)s_lut[(wr.octinv << 8) | (hits & imask)] << 24) | imask);
                     tm = hits & lmask; tri_lmask = lmask;
+                    if (tm != 0u && (pk & 0xffu) == 0u) { pk = tm | (lmask << 8); ptri_base = tri_base; tm = 0u; }
                 }
             }
             // ---- triangle phase: one parked triangle per lane, once enough lanes have one ----
-            const int n_tri = __popc(__ballot_sync(0xffffffffu, has && tm != 0u));
+            const int n_tri = __popc(__ballot_sync(0xffffffffu, has && (pk & 0xffu) != 0u));
             const int n_node = __popc(__ballot_sync(0xffffffffu, has && tm == 0u && ((G.y & 0xff000000u) || sp > 0)));
-            if (n_tri >= WF_TRI_BATCH || (n_tri > 0 && n_node == 0)) {
-                if (has && tm != 0u) {
-                    const int b = __ffs((int)tm) - 1;
-                    tm &= tm - 1u;
-                    const float4* t = &WB.tris[3 * (size_t)(tri_base + (uint32_t)__popc(tri_lmask & ~(0xffffffffu << b)))];
+                        if (n_tri >= WF_TRI_BATCH || (n_tri > 0 && n_tri * WF_TRI_ADAPT >= n_node)) {
+                if (has && (pk & 0xffu) != 0u) {
+                    const int b = __ffs((int)pk) - 1;
+                    const float4* t = &WB.tris[3 * (size_t)(ptri_base + (uint32_t)__popc((pk >> 8) & ~(0xffffffffu << b)))];
+                    pk &= pk - 1u;
+                    if ((pk & 0xffu) == 0u) { pk = tm | (tri_lmask << 8); ptri_base = tri_base; tm = 0u; }     // next set (possibly empty)
                     const float4 A = __ldg(&t[0]), B = __ldg(&t[1]), C = __ldg(&t[2]);
                     oc.fetch(S, __float_as_int(B.w), ray);
                     float dst, uu, vv;
@@ -185,38 +226,9 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     }
                 }
             }
-            // ---- lanes whose walk is over write their result back and free the lane ----
-            if (has && tm == 0u && !(G.y & 0xff000000u) && sp == 0) {
-                if (ambiguous | tie) {
-                    // equal-distance triangles or a stack overflow: the reference-order walk decides.  The slot
-                    // still holds the ray and its sphere/quad result; it is only MARKED here and the shade stage
-                    // resolves it (inline, one such ray stalled the other 31 lanes of this warp for the length
-                    // of a latency-bound binary walk; in shade the other warps of the SM hide that latency).
-                    // A tie carries the closest distance along, an overflow of the wide stack does not.
-                    if (!ambiguous) reinterpret_cast<float*>(&P.pool.x[slot])[2] = closest;
-                    reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = (tag0 & ~0xf0u) | ((uint32_t)(ambiguous ? WF_CLS_OVERFLOW : WF_CLS_TIE) << 4);
-                } else {
-                    const bool hit = hit_a | hit_t;
-                    const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
-                    uint32_t tag = (tag0 & ~0xf0u) | ((uint32_t)cls << 4);          // the sphere/quad hit (or the miss) stands
-                    if (hit_t) {
-                        tag = wf_tag(HIT_TRI, cls, h.mat_id);
-                        reinterpret_cast<float*>(&P.pool.e0[slot])[3] = h.t;
-                        P.pool.x[slot] = make_float4(__uint_as_float(tag), __int_as_float(h.index), h.uu, h.vv);
-                    } else {
-                        reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = tag;
-                    }
-                    if (P.prim_type) {
-                        const float4 e1v = P.pool.e1[slot], s1v = P.pool.s1[slot];
-                        if ((__float_as_uint(e1v.w) & 0x03ffffffu) == 0u) {                // first query of the item: the primary ray
-                            if (!hit_t) h.index = __float_as_int(P.pool.x[slot].y);
-                            write_probe(S, P, __float_as_uint(s1v.w), hit, h);
-                        }
-                    }
-                }
-                has = false;
-            }
-            const int active = __popc(__ballot_sync(0xffffffffu, has));
+            // a lane whose walk is over idles until the warp refills; its result is written back then, together
+            // with the other finished lanes (done one by one as each lane finished, that code ran 2 lanes wide)
+            const int active = __popc(__ballot_sync(0xffffffffu, has && (tm != 0u || (pk & 0xffu) != 0u || (G.y & 0xff000000u) || sp > 0)));
             if (active == 0) break;
             if (!exhausted && active < WF_REFILL_BELOW) break;
         }
