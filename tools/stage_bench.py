@@ -25,6 +25,6 @@ for cfg in cfgs:
     ms, launches, st = best
     fs = pt.fast_statistics()
     print("%s %d frames: %.3f ms/frame  %.1f Msamples/s  launches=%d iters=%d fallbacks=%d | %s" % (
-        cfg, frames, ms / frames, W * H * kw.get("num_samples", 1) * frames / ms / 1e3, launches, fs["iterations"], fs["fallback_rays"],
+        cfg + " levels=%d" % fs["wide_levels"], frames, ms / frames, W * H * kw.get("num_samples", 1) * frames / ms / 1e3, launches, fs["iterations"], fs["fallback_rays"],
         "  ".join("%s %.2f ms (%d)" % (k, v[0], v[1]) for k, v in st.items())), flush=True)
     pt.close()

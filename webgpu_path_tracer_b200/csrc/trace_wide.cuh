@@ -15,7 +15,9 @@
 
 namespace wg {
 
+#ifndef WIDE_STACK
 #define WIDE_STACK 24
+#endif
 
 struct WideRay {
     float idx, idy, idz;      // 1/d with tiny components clamped (box tests only)
