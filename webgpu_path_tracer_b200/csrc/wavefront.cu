@@ -168,6 +168,11 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                         hit_a = h.kind != HIT_NONE;
                         closest = hit_a ? o4.w : WGPT_MAX_FLOAT;
                         oc.reset();
+#ifndef WF_NO_OBJRAY_AT_FETCH
+                        // One mesh in the scene: its object-space ray (common.wgsl:193-197) is set up here, where at least
+                        // a third of the warp fetches together; done lazily at the first triangle test it ran ~4 lanes wide.
+                        if (S.NUM_MESHES == 1) oc.fetch(S, 0, ray);
+#endif
                         hit_t = false; ambiguous = false; tie = false; sp = 0; tm = 0; pk = 0;
                         wr = make_wide_ray(ray);
                         G = make_uint2(0u, 0x80000000u);
