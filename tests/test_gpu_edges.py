@@ -1,0 +1,116 @@
+"""Edge cases of the hot path on the GPU, through the C ABI, bit-exact against the CPU oracle: scenes with no
+triangles / nothing at all, image sizes that are no multiple of a workgroup or a tile, several meshes with
+different transforms, a traversal stack small enough for the reference's guard (hitRay.wgsl:100-104) to fire,
+the lowest bounce limits, and tile shards that must add up to the unsharded image."""
+import numpy as np
+import pytest
+
+from webgpu_path_tracer_b200 import PathTracer, Scene, Camera, MODE_EXACT, MODE_FAST
+from oracle.binding import Oracle
+from tests import scenes
+from tests.util import bits
+
+pytestmark = pytest.mark.gpu
+
+
+def setup(x, scene, cam, frame=1):
+    x.write_scene(scene.buffers())
+    x.write_uniforms(frame, 0, cam.viewMatrix)
+    return x
+
+
+def check_all_modes(scene, cam, W, H, frames=3, **kw):
+    o = setup(Oracle(W, H, **kw), scene, cam)
+    ro, to, io, do = o.probe()
+    o.render(1, frames)
+    fo = o.read_framebuffer()
+    for mode in (MODE_EXACT, MODE_FAST):
+        g = setup(PathTracer(W, H, mode=mode, **kw), scene, cam)
+        rg, tg, ig, dg = g.probe()
+        assert int((to != tg).sum() + (io != ig).sum()) == 0, mode
+        assert np.array_equal(bits(do), bits(dg)), mode
+        assert np.array_equal(bits(ro), bits(rg)), mode
+        g.render(1, frames)
+        assert np.array_equal(bits(fo), bits(g.read_framebuffer())), mode
+        g.close()
+    return fo
+
+
+def room_only():
+    s = Scene(default=False)
+    s.add_sphere([0.3, -0.6, 0.1], 0.4, s.add_material("ball", *scenes.MIRROR_MAT))
+    s.add_sphere([-0.4, -0.7, -0.3], 0.3, s.add_material("glass", *scenes.GLASS_MAT))
+    s.objs.append(list(s.spheres))
+    scenes.cornell_room(s)
+    cam = Camera()
+    cam.set_camera([0, 0, 2.5], [0, 0, 0], [0, 1, 0])
+    return s, cam
+
+
+@pytest.mark.parametrize("W,H", [(37, 23), (64, 1), (1, 64), (130, 67)])
+def test_scene_without_triangles_and_ragged_image_sizes(W, H):
+    """No mesh, no BVH (bindings 5, 6, 7, 9 empty): the traversal stage has nothing to do; sizes that are
+    no multiple of the 64-thread workgroup (renderer.js:187-188 dispatches W*H/64 + 1 groups) or of a tile."""
+    scene, cam = room_only()
+    check_all_modes(scene, cam, W, H)
+
+
+def test_empty_scene_is_all_background():
+    s = Scene(default=False)
+    cam = Camera()
+    cam.set_camera([0, 0, 2.5], [0, 0, 0], [0, 1, 0])
+    fb = check_all_modes(s, cam, 48, 32, frames=2)
+    fb = np.asarray(fb).reshape(-1, 4)
+    assert np.array_equal(fb[:, :3], np.tile(np.float32([0, 2, 2]), (48 * 32, 1)))          # traceRay.wgsl:12-16, two frames
+
+
+def test_two_meshes_with_different_transforms(golden_meshes):
+    """Two meshes, two materials, two inverse model matrices: the object-space ray is per (ray, mesh)
+    (common.wgsl:193-197) and a ray may test triangles of both."""
+    s = Scene(default=False)
+    scenes.cornell_room(s)
+    for name, mat, tr in (("monkey_968", scenes.DRAGON_MAT, [("scale", 0.45, 0.45, 0.45), ("rotate", 0.6, [0, 1, 0]), ("translate", -0.45, -0.4, 0.1)]),
+                          ("icosphere", scenes.GLASS_MAT, [("scale", 0.4, 0.5, 0.4), ("translate", 0.45, -0.3, -0.2)])):
+        data = {"vertices": golden_meshes[name + "_vertices"], "normals": golden_meshes[name + "_normals"]}
+        m = s.add_mesh(data, s.add_material(name, *mat))
+        m.transform.update(*[getattr(m.transform, t[0])(*t[1:]) for t in tr])
+    s.create_meshes()
+    s.create_bvh()
+    cam = Camera()
+    cam.set_camera([0, 0, 2.5], [0, 0, 0], [0, 1, 0])
+    check_all_modes(s, cam, 128, 80, importance_sampling=True)
+
+
+def test_stack_guard_of_the_reference_fires_identically(golden_meshes):
+    """STACK_SIZE below the tree depth: the reference's walk aborts when its stack would overflow
+    (hitRay.wgsl:100-104) and returns whatever it had; the fast path must fall back to that very walk."""
+    data = {"vertices": golden_meshes["monkey_968_vertices"], "normals": golden_meshes["monkey_968_normals"]}
+    scene, cam = scenes.mesh_in_room(data, scenes.DRAGON_MAT, [("scale", 0.7, 0.7, 0.7), ("translate", 0, -0.3, 0)])
+    for stack_size in (4, 7):
+        check_all_modes(scene, cam, 96, 64, frames=2, stack_size=stack_size)
+
+
+@pytest.mark.parametrize("max_bounces", [1, 2])
+def test_lowest_bounce_limits(default_scene, max_bounces):
+    scene, cam = default_scene
+    check_all_modes(scene, cam, 80, 48, frames=2, max_bounces=max_bounces)
+
+
+def test_tile_shards_add_up_to_the_unsharded_image(default_scene):
+    """interleaved row-block shards render disjoint pixels in frame order, so their
+    framebuffers add up (zeros elsewhere) to the single-GPU image bit for bit; 3 shards, 5-row tiles, a
+    height that is no multiple of either."""
+    scene, cam = default_scene
+    W, H, frames = 96, 53, 3
+    whole = setup(PathTracer(W, H, mode=MODE_FAST), scene, cam)
+    whole.render(1, frames)
+    ref = np.asarray(whole.read_framebuffer()).reshape(-1, 4)
+    total = np.zeros_like(ref)
+    for r in range(3):
+        g = setup(PathTracer(W, H, mode=MODE_FAST, tile_rank=r, tile_world=3, tile_rows=5), scene, cam)
+        g.render(1, frames)
+        part = np.asarray(g.read_framebuffer()).reshape(-1, 4)
+        assert not np.any((part[:, 3] != 0) & (total[:, 3] != 0))                      # shards are disjoint
+        total += part
+        g.close()
+    assert np.array_equal(bits(ref), bits(total))

@@ -127,8 +127,9 @@ static int ensure_wide(wgpt_ctx* c) {
     return WGPT_OK;
 }
 
-static WideBvh wide_view(FastState* F) {
+static WideBvh wide_view(const wgpt_ctx* c, FastState* F) {
     WideBvh w; w.nodes = F->wide_nodes; w.tris = F->wide_tris; w.n_nodes = F->wstats.n_nodes; w.n_tris = F->wstats.n_tris;
+    w.force_reference_walk = c->bvh_depth >= std::min(c->cfg.stack_size, 64) ? 1u : 0u;
     return w;
 }
 
@@ -203,7 +204,7 @@ int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_firs
     P.bvh_depth = c->bvh_depth;
     P.prim_type = d_ptype; P.prim_index = d_pindex; P.prim_t = d_pt;
     const DeviceScene S = make_device_scene(c, 0xffffffffu);
-    const WideBvh WB = wide_view(F);
+    const WideBvh WB = wide_view(c, F);
     wf_launch_init(P, my_frames, c->stream);
     c->last_launches += 1;
     const int batch = std::max(1, env_int("WGPT_BATCH", 8));
@@ -239,7 +240,7 @@ int fast_trace_rays(wgpt_ctx* c, int n, const float* d_rays, const uint32_t* d_s
     }
     if (!c->have_uniforms) memset(&c->uniforms, 0, sizeof(c->uniforms));
     const DeviceScene S = make_device_scene(c, 0xffffffffu);
-    launch_trace_rays_wide(S, wide_view(F), n, d_rays, d_seeds, d_type, d_index, d_t, F->d_fallbacks, c->stream);
+    launch_trace_rays_wide(S, wide_view(c, F), n, d_rays, d_seeds, d_type, d_index, d_t, F->d_fallbacks, c->stream);
     return cuda_err(c, cudaGetLastError(), "fast_trace_rays");
 }
 

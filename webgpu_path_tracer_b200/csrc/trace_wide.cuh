@@ -122,6 +122,7 @@ __device__ __forceinline__ bool hit_bvh_wide(const DeviceScene& S, const WideBvh
                                              Counts* cnt, ObjRayCache& oc, float& closest, HitLite& h, bool& ambiguous) {
     ambiguous = false;
     if (WB.n_nodes == 0) return false;
+    if (WB.force_reference_walk) { ambiguous = true; return false; }
     const WideRay wr = make_wide_ray(ray);
     const unsigned char* lut_r = lut + (wr.octinv << 8);
     bool hit_anything = false;

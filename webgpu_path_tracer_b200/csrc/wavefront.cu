@@ -176,6 +176,7 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                         hit_t = false; ambiguous = false; tie = false; sp = 0; tm = 0; pk = 0;
                         wr = make_wide_ray(ray);
                         G = make_uint2(0u, 0x80000000u);
+                        if (WB.force_reference_walk) { ambiguous = true; G.y = 0u; }     // marked at once: the reference walk decides
                         has = true;
                     }
                 }

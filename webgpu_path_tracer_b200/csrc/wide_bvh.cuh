@@ -33,6 +33,9 @@ struct WideBvh {
     const uint4* nodes;       // 5 uint4 per node; node 0 is the root
     const float4* tris;       // 3 float4 per packed triangle
     uint32_t n_nodes, n_tris;
+    // The reference's stack guard (hitRay.wgsl:100-104) can fire: binding 9 is at least STACK_SIZE deep, so what
+    // the reference returns depends on its own visit order for ANY ray.  Every ray then takes the reference walk.
+    uint32_t force_reference_walk;
 };
 
 struct WideBuildStats { uint32_t n_nodes, n_tris, n_levels, overflow; };
