@@ -114,3 +114,70 @@ def test_tile_shards_add_up_to_the_unsharded_image(default_scene):
         total += part
         g.close()
     assert np.array_equal(bits(ref), bits(total))
+
+
+def synthetic_mesh(kind, seed=5):
+    """Triangle soups that stress the hierarchy build and the quantised boxes."""
+    rng = np.random.default_rng(seed)
+    if kind == "duplicates_and_degenerates":
+        # every triangle twice (an exact tie on every hit), plus zero-area and zero-extent triangles
+        base = rng.uniform(-0.6, 0.6, (60, 1, 3)).astype(np.float32) + rng.uniform(-0.25, 0.25, (60, 3, 3)).astype(np.float32)
+        line = np.stack([base[:8, 0], base[:8, 1], (base[:8, 0] + base[:8, 1]) * np.float32(0.5)], axis=1)     # collinear
+        point = np.repeat(base[8:12, :1], 3, axis=1)                                                                # a single point
+        v = np.concatenate([base, base, line, point], axis=0)
+    elif kind == "flat":
+        # all triangles in the plane z = 0.125: every box has zero extent in z (the reference pads it, AABB.js:35-51)
+        xy = rng.uniform(-0.8, 0.8, (200, 1, 2)).astype(np.float32) + rng.uniform(-0.15, 0.15, (200, 3, 2)).astype(np.float32)
+        v = np.concatenate([xy, np.full((200, 3, 1), 0.125, np.float32)], axis=2)
+    elif kind == "scale_disparity":
+        # two huge triangles spanning the room and a cloud of tiny ones: one quantisation frame holds both scales
+        big = np.float32([[[-0.95, -0.9, -0.5], [0.95, -0.9, -0.5], [0.0, 0.9, -0.45]],
+                          [[-0.95, -0.9, 0.2], [0.0, 0.9, 0.25], [0.95, -0.9, 0.2]]])
+        c = rng.uniform(-0.5, 0.5, (400, 1, 3)).astype(np.float32)
+        tiny = c + rng.uniform(-2e-3, 2e-3, (400, 3, 3)).astype(np.float32)
+        v = np.concatenate([big, tiny], axis=0)
+    else:
+        raise KeyError(kind)
+    v = np.ascontiguousarray(v, np.float32)
+    e1, e2 = v[:, 1] - v[:, 0], v[:, 2] - v[:, 0]
+    n = np.cross(e1, e2)
+    ln = np.linalg.norm(n, axis=1, keepdims=True)
+    n = np.where(ln > 0, n / np.maximum(ln, 1e-30), np.float32([0, 0, 1])).astype(np.float32)
+    return {"vertices": v.reshape(-1), "normals": np.repeat(n[:, None, :], 3, axis=1).reshape(-1)}
+
+
+@pytest.mark.parametrize("kind", ["duplicates_and_degenerates", "flat", "scale_disparity"])
+def test_hard_triangle_soups(kind):
+    scene, cam = scenes.mesh_in_room(synthetic_mesh(kind), scenes.DRAGON_MAT, [("rotate", 0.3, [0, 1, 0])])
+    check_all_modes(scene, cam, 128, 96, frames=2)
+    rays, seeds = scenes.random_rays(200_000, 11)
+    e = setup(PathTracer(8, 8, mode=MODE_EXACT), scene, cam)
+    g = setup(PathTracer(8, 8, mode=MODE_FAST), scene, cam)
+    te, ie, de = e.trace_rays(rays, seeds)
+    tg, ig, dg = g.trace_rays(rays, seeds)
+    assert int((te != tg).sum()) == 0 and int((ie != ig).sum()) == 0
+    assert np.array_equal(bits(de), bits(dg))
+
+
+def test_scene_far_from_the_origin(golden_meshes):
+    """Everything translated by (1000, -500, 250): f32 coordinates lose 10 bits, the quantisation frames sit on
+    large origins, the reference's +-5e-5 box pad falls below one ulp of the coordinates."""
+    off = np.float32([1000.0, -500.0, 250.0])
+    s = Scene(default=False)
+    am = s.add_material
+    s.add_sphere(list(np.float32([0.4, -0.6, 0.2]) + off), 0.35, am("ball", *scenes.MIRROR_MAT))
+    s.objs.append(list(s.spheres))
+    e = 20.0
+    s.add_quad(list(np.float32([-0.35, 0.9999, -0.25]) + off), [0.7, 0, 0], [0, 0, 0.5], am("light", 0, [0, 0, 0], [0, 0, 0], [e, e, e], 0, 0, 0))
+    s.add_quad(list(np.float32([-1, -1, -1]) + off), [2, 0, 0], [0, 2, 0], am("back", 0, [0.7, 0.7, 0.7], [0.7, 0.7, 0.7], [0, 0, 0], 0.05, 0.95, 0))
+    s.add_quad(list(np.float32([-1, -1, -1]) + off), [2, 0, 0], [0, 0, 2], am("floor", 0, [0.6, 0.6, 0.3], [0.6, 0.6, 0.3], [0, 0, 0], 0.05, 0.95, 0))
+    s.lights.append(s.quads[0])
+    s.objs.append(list(s.quads))
+    data = {"vertices": golden_meshes["monkey_968_vertices"], "normals": golden_meshes["monkey_968_normals"]}
+    m = s.add_mesh(data, am("meshMat", *scenes.DRAGON_MAT))
+    m.transform.update(m.transform.scale(0.6, 0.6, 0.6), m.transform.translate(float(off[0]), float(off[1]) - 0.3, float(off[2])))
+    s.create_meshes()
+    s.create_bvh()
+    cam = Camera()
+    cam.set_camera(list(np.float32([0, 0, 2.5]) + off), list(off), [0, 1, 0])
+    check_all_modes(s, cam, 128, 96, frames=2)
