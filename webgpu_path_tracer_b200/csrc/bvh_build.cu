@@ -20,7 +20,9 @@
 
 namespace wg {
 
+#ifndef PLOC_R
 #define PLOC_R 16               // neighbours searched on each side
+#endif
 #define PLOC_TAIL 1024          // cluster count handed to the single-block kernel
 #define PLOC_GLOBAL_ITERS 28
 #define NONE 0xffffffffu
