@@ -57,7 +57,7 @@ typedef struct wgpt_config {
     int32_t  width, height;        /* canvas size; uniforms.screenDims must match */
     int32_t  device;               /* CUDA device ordinal */
     int32_t  mode;                 /* WGPT_MODE_* */
-    int32_t  num_samples;          /* NUM_SAMPLES          (reference HEAD: 1)   */
+    int32_t  num_samples;          /* NUM_SAMPLES          (reference HEAD: 1); fast mode: <= 16383 */
     int32_t  max_bounces;          /* MAX_BOUNCES          (100)                 */
     int32_t  stratify;             /* STRATIFY             (false)               */
     int32_t  importance_sampling;  /* IMPORTANCE_SAMPLING  (false)               */

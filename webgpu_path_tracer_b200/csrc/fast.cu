@@ -140,7 +140,11 @@ static int ensure_pool(wgpt_ctx* c) {
     uint32_t cap = (uint32_t)env_int("WGPT_POOL", 0);
     if (!cap) cap = std::min<uint64_t>(1u << 23, (uint64_t)c->shard_pixels * 4);
     cap = std::max(1024u, (cap + 1023u) & ~1023u);
-    uint32_t ring = (uint32_t)env_int("WGPT_RING", 64);
+    // Frames in flight: a frame is folded into binding 3 only when its slowest path has ended (up to MAX_BOUNCES
+    // iterations later), so the window must be long enough to keep the slots fed meanwhile: 8 GiB of staging,
+    // between 64 and 256 frames (1080p: 256 frames; 4K: 64).
+    uint32_t ring = (uint32_t)env_int("WGPT_RING", 0);
+    if (!ring) ring = (uint32_t)std::min<uint64_t>(WF_MAX_RING, std::max<uint64_t>(64, (8ull << 30) / ((uint64_t)npix * 16)));
     ring = std::max(2u, std::min<uint32_t>(ring, WF_MAX_RING));
     // one allocation, carved into 16-byte-aligned arrays
     const size_t per_slot = WF_BYTES_PER_SLOT;
@@ -187,8 +191,8 @@ static int check_materials(wgpt_ctx* c) {
 int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_first, int* d_ptype, int* d_pindex, float* d_pt) {
     int rc = check_materials(c);
     if (rc) return rc;
-    if (c->cfg.max_bounces > WF_MAX_BOUNCE_FIELD || c->cfg.num_samples > 65535)
-        return set_err(c, WGPT_E_INVALID, "fast mode packs the bounce / sample counters: max_bounces <= 1023, num_samples <= 65535");
+    if (c->cfg.max_bounces > WF_MAX_BOUNCE_FIELD || c->cfg.num_samples > WF_MAX_SAMPLE_FIELD)
+        return set_err(c, WGPT_E_INVALID, "fast mode packs the bounce / sample counters: max_bounces <= 1023, num_samples <= 16383");
     if ((rc = ensure_wide(c)) != WGPT_OK) return rc;
     if ((rc = ensure_pool(c)) != WGPT_OK) return rc;
     FastState* F = c->fast;

@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                 }
                 if (P.prim_type) {
                     const float4 e1v = P.pool.e1[slot], s1v = P.pool.s1[slot];
-                    if ((__float_as_uint(e1v.w) & 0x03ffffffu) == 0u) {                // first query of the item: the primary ray
+                    if ((__float_as_uint(e1v.w) & WF_CTR_FIRST_QUERY_MASK) == 0u) {                // first query of the item: the primary ray
                         if (!hit_t) h.index = __float_as_int(P.pool.x[slot].y);
                         write_probe(S, P, __float_as_uint(s1v.w), hit, h);
                     }
@@ -296,7 +296,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     WfControl* ctl = P.ctl;
     if (ctl->finished) return;                             // the host notices the flag one batch late: those launches are empty
     const uint32_t lane = threadIdx.x & 31u;
-    if (threadIdx.x < WF_MAX_RING) s_done[threadIdx.x] = 0;
+    for (uint32_t k = threadIdx.x; k < WF_MAX_RING; k += blockDim.x) s_done[k] = 0;
     if (threadIdx.x == 0) { s_qn = 0; s_arrived = 0; }
 
     // ---- material sort inside the block: slot (block base + j) -> thread rank by shade key ----
@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         }
         atomicAdd(&ctl->fallbacks, 1u);
         if (P.prim_type) {
-            if ((__float_as_uint(e1v.w) & 0x03ffffffu) == 0u) write_probe(S, P, __float_as_uint(s1v.w), hit, h);
+            if ((__float_as_uint(e1v.w) & WF_CTR_FIRST_QUERY_MASK) == 0u) write_probe(S, P, __float_as_uint(s1v.w), hit, h);
         }
     }
 
@@ -394,7 +394,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         bool ended = false;
         const uint32_t ctr = __float_as_uint(e1v.w);
         rng = __float_as_uint(s1v.z); pix_i = __float_as_uint(s1v.w);
-        ring_slot = ctr >> 26; bounce = (ctr >> 16) & 0x3ffu; scnt = ctr & 0xffffu;
+        ring_slot = ctr >> 24; bounce = (ctr >> 14) & 0x3ffu; scnt = ctr & 0x3fffu;
         thr = V3(s0v.x, s0v.y, s0v.z); acc = V3(s0v.w, s1v.x, s1v.y);
         if (cls == WF_CLS_MISS) {                             // traceRay.wgsl:12-16
             acc = acc + V3(0.0f, 1.0f, 1.0f) * thr;
@@ -507,7 +507,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         P.pool.s1[slot] = make_float4(acc.y, acc.z, __uint_as_float(rng), __uint_as_float(pix_i));
         P.pool.x[slot] = make_float4(__uint_as_float(wf_tag(hit_a ? h.kind : (int)HIT_NONE, ncls, h.mat_id)), __int_as_float(h.index), 0.0f, 0.0f);
         if (store_pix) P.pool.pix[slot] = pix;
-        if (!trace && P.prim_type && (ctr & 0x03ffffffu) == 0u) write_probe(S, P, pix_i, hit_a, h);
+        if (!trace && P.prim_type && (ctr & WF_CTR_FIRST_QUERY_MASK) == 0u) write_probe(S, P, pix_i, hit_a, h);
     } else if (cls <= WF_CLS_IDLE && new_cls != cls) {
         reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = wf_tag(HIT_NONE, new_cls, -1);    // idle (waiting for the window) or dead (no work left)
     }
@@ -535,7 +535,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
             if (lane == 0 && total) base = atomicAdd(&ctl->n_next, total);
             base = __shfl_sync(0xffffffffu, base, 0);
             for (uint32_t i = lane; i < total; i += 32) P.q_extend[base + i] = ((volatile uint32_t*)s_q)[i];
-            for (uint32_t k = lane; k < WF_MAX_RING; k += 32) {
+            for (uint32_t k = lane; k < P.ring; k += 32) {
                 const uint32_t v = ((volatile uint32_t*)s_done)[k];
                 if (v) atomicAdd(&ctl->done[k], v);
             }

@@ -10,7 +10,7 @@
 
 namespace wg {
 
-#define WF_MAX_RING 64
+#define WF_MAX_RING 256
 // slot status / shade class, kept in hid.w: 0..3 = material_type of the hit to shade, 4 = miss to
 // shade, 5 = idle (no path; waiting for the ring window to release work), 6 = dead (no path, no
 // work left), 7 = in the extend queue
@@ -31,7 +31,7 @@ namespace wg {
 //        the hit's data (triangle normals, material), so all further loads can be issued at once.
 //        For WF_CLS_TIE the u lane carries the closest distance the extend stage found.
 //   e0 = (ray origin.xyz, hit t)
-//   e1 = (ray direction.xyz, counters)                 counters = (ring slot << 26) | (bounce << 16) | sample
+//   e1 = (ray direction.xyz, counters)                 counters = (ring slot << 24) | (bounce << 14) | sample
 //   s0 = (throughput.xyz, radiance.x)
 //   s1 = (radiance.y, radiance.z, rng state, shard-local pixel)
 // The extend stage reads e0, e1 and x.tag and writes x (and the t lane of e0) when a triangle wins.
@@ -42,12 +42,14 @@ struct PathPool {
 };
 #define WF_BYTES_PER_SLOT (6 * 16 + 4)      /* 6 records + one ray-queue entry */
 #define WF_MAX_BOUNCE_FIELD 1023
+#define WF_MAX_SAMPLE_FIELD 16383
+#define WF_CTR_FIRST_QUERY_MASK 0x00ffffffu   /* bounce == 0 and sample == 0: the primary ray of the item */
 
 __host__ __device__ inline uint32_t wf_tag(int kind, int cls, int mat_id) { return ((uint32_t)mat_id << 8) | ((uint32_t)cls << 4) | (uint32_t)(kind + 1); }
 __host__ __device__ inline int wf_tag_kind(uint32_t tag) { return (int)(tag & 15u) - 1; }
 __host__ __device__ inline int wf_tag_cls(uint32_t tag) { return (int)((tag >> 4) & 15u); }
 __host__ __device__ inline int wf_tag_mat(uint32_t tag) { return (int)(tag >> 8) == 0xffffff ? -1 : (int)(tag >> 8); }
-__host__ __device__ inline uint32_t wf_ctr(uint32_t ring_slot, uint32_t bounce, uint32_t scnt) { return (ring_slot << 26) | (bounce << 16) | (scnt & 0xffffu); }
+__host__ __device__ inline uint32_t wf_ctr(uint32_t ring_slot, uint32_t bounce, uint32_t scnt) { return (ring_slot << 24) | (bounce << 14) | (scnt & 0x3fffu); }
 
 struct WfControl {
     unsigned long long next_work;      // next (frame ordinal, pixel) item to hand out
