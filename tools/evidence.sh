@@ -8,6 +8,10 @@ mkdir -p $O
 timeout 900 python -m pytest tests -m gpu -x -q > $O/pytest_gpu_$R.log 2>&1; echo "pytest rc=$?" | tee -a $O/pytest_gpu_$R.log
 timeout 900 python bench.py --steps 5 --warmup 3 > $O/bench_$R.json 2> $O/bench_err.log; echo "bench rc=$?"
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref_$R.json 2>> $O/bench_err.log; echo "bench ref rc=$?"
+timeout 200 python bench.py --config C1 --steps 5 --warmup 3 > $O/bench_C1_$R.json 2>> $O/bench_err.log
+timeout 300 python bench.py --config C3 --steps 3 --warmup 3 --cpu-baseline-frames 4 > $O/bench_C3_$R.json 2>> $O/bench_err.log
+timeout 500 python bench.py --config C4 --steps 2 --warmup 3 --cpu-baseline-frames 4 > $O/bench_C4_$R.json 2>> $O/bench_err.log
+timeout 120 python tools/visit_stats.py C1,C2,C3,C4,C5 2 > $O/visits_$R.txt 2>&1
 timeout 120 python tools/k4_bench.py > $O/k4_$R.txt 2>&1
 timeout 300 python tools/stage_bench.py C1,C2,C3,C4,C5 64 > $O/stages_$R.txt 2>&1
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file $O/launches_$R.csv \
