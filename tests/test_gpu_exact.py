@@ -90,3 +90,13 @@ def test_device_only_math_forms_equal_the_plain_ones():
     a = (rng.uniform(-1, 1, 1_000_000) * 7.0).astype(np.float32)
     assert np.array_equal(bits(g.pinned_math("sincos_sin", a)), bits(pinned_math("sin", a)))
     assert np.array_equal(bits(g.pinned_math("sincos_cos", a)), bits(pinned_math("cos", a)))
+
+
+def test_k4_stream_timing_hook_reports_time_and_bytes():
+    """wgpt_k4_timing (the roofline hook of the accumulate / present passes) leaves binding 3 alone."""
+    g = PathTracer(256, 128, mode=MODE_EXACT)
+    before = np.asarray(g.read_framebuffer()).copy()
+    for kernel, per_px in (("accumulate", 48), ("present_rgba8", 20), ("present_f32", 32)):
+        ms, nbytes = g.k4_timing(kernel, reps=5)
+        assert ms > 0.0 and nbytes == 256 * 128 * per_px
+    assert np.array_equal(before, np.asarray(g.read_framebuffer()))

@@ -266,8 +266,11 @@ int wgpt_k4_timing(wgpt_ctx* c, int kernel, int reps, float* ms_per_launch, uint
         cudaMemcpyAsync(d_frame.p, h.data(), h.size() * 4, cudaMemcpyHostToDevice, c->stream);
         cudaStreamSynchronize(c->stream);
     }
-    cudaEvent_t a, b;
-    cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEvent_t a = nullptr, b = nullptr;
+    if ((e = cudaEventCreate(&a)) != cudaSuccess || (e = cudaEventCreate(&b)) != cudaSuccess) {
+        if (a) cudaEventDestroy(a);
+        return cuda_err(c, e, "k4_timing");
+    }
     for (int pass = 0; pass < 2; pass++) {                                   // pass 0 = warm-up
         if (pass) cudaEventRecord(a, c->stream);
         for (int r = 0; r < (pass ? reps : 3); r++) {
