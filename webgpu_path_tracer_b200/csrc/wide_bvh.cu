@@ -6,6 +6,7 @@
 // with prim_count == 1; the subtree of i spans [i, skip_link >= 0 ? skip_link : N) and therefore
 // holds (end - i + 1) / 2 triangles.
 #include "wide_bvh.cuh"
+#include <cstdlib>
 
 namespace wg {
 
@@ -18,6 +19,15 @@ struct BuildCtx {
     uint32_t max_nodes;
     uint32_t* counters;      // [0] nodes, [1] tris, [2],[3] queue counts, [4] levels, [5] overflow
     uint2* queue[2];
+    // collapse plan (k_plan_*): which binary nodes become the children of a wide node
+    int use_plan;
+    int* parent;             // binary parent of every node (-1 for the root)
+    uint32_t* arrived;       // bottom-up rendezvous counters
+    float* cost;             // 8 floats per binary node: cost[i][k-1] = least summed area of the wide nodes that
+                             // represent subtree i when it may occupy at most k slots of its wide parent
+    uint2* plan;             // x: 4 bits per k = 2..8, the choice behind cost[i][k-1] (1 = i stays one inner child,
+                             //    j = i is opened and its two subtrees share j slots); y: 3 bits per j = 2..8, how many
+                             //    of the j slots the left subtree gets
 };
 
 __device__ __forceinline__ int sub_end(const BuildCtx& B, int i) {
@@ -38,6 +48,70 @@ __global__ void k_wide_init(BuildCtx B) {
     }
 }
 
+// ---- SAH-optimal collapse plan -------------------------------------------------------------------
+// The expected number of wide-node visits of a random ray is the summed surface area of the wide nodes
+// (the triangle tests do not depend on the collapse: every triangle is one leaf slot whatever the shape).
+// Largest-area-first expansion approximates that sum; the dynamic programme below minimises it exactly
+// for the given binary tree (Ylitie, Karras, Laine 2017, section 3.2, with one-triangle leaves):
+//   cost(i, 1) = area(i) + open(i, 8)                      i becomes a wide node of its own
+//   cost(i, k) = min(cost(i, k-1), open(i, k))             or its subtrees take k slots of the wide parent
+//   open(i, j) = min over a + b = j of cost(left, a) + cost(right, b);   cost(leaf, k) = 0
+// evaluated bottom-up (one thread per leaf climbs; the second thread to arrive at a node evaluates it).
+__global__ void k_plan_parents(BuildCtx B) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B.n_bvh) return;
+    if (i == 0) B.parent[0] = -1;
+    if (is_leaf(B, i)) return;
+    const int r = (int)B.bvh[i].right_offset;
+    if (i + 1 < B.n_bvh) B.parent[i + 1] = i;
+    if (r > i && r < B.n_bvh) B.parent[r] = i;
+}
+
+__global__ void k_plan_costs(BuildCtx B) {
+    const int leaf = blockIdx.x * blockDim.x + threadIdx.x;
+    if (leaf >= B.n_bvh || !is_leaf(B, leaf)) return;
+    float4* cost4 = reinterpret_cast<float4*>(B.cost);
+    cost4[2 * (size_t)leaf] = make_float4(0.f, 0.f, 0.f, 0.f);
+    cost4[2 * (size_t)leaf + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    int cur = leaf;
+    for (int guard = 0; guard < 4096; guard++) {
+        const int p = cur > 0 ? B.parent[cur] : -1;
+        if (p < 0 || p >= B.n_bvh) return;
+        __threadfence();
+        if (atomicAdd(&B.arrived[p], 1u) == 0u) return;          // the sibling subtree is not done yet: its thread goes on
+        __threadfence();
+        const int l = p + 1, r = (int)B.bvh[p].right_offset;
+        if (r <= l || r >= B.n_bvh) return;                      // not the flatten contract: k_wide_level reports it
+        float cl[9], cr[9];
+        {
+            const float4 a0 = __ldcg(&cost4[2 * (size_t)l]), a1 = __ldcg(&cost4[2 * (size_t)l + 1]);
+            const float4 b0 = __ldcg(&cost4[2 * (size_t)r]), b1 = __ldcg(&cost4[2 * (size_t)r + 1]);
+            cl[1] = a0.x; cl[2] = a0.y; cl[3] = a0.z; cl[4] = a0.w; cl[5] = a1.x; cl[6] = a1.y; cl[7] = a1.z; cl[8] = a1.w;
+            cr[1] = b0.x; cr[2] = b0.y; cr[3] = b0.z; cr[4] = b0.w; cr[5] = b1.x; cr[6] = b1.y; cr[7] = b1.z; cr[8] = b1.w;
+        }
+        float open[9]; uint32_t splits = 0;
+        #pragma unroll
+        for (int j = 2; j <= 8; j++) {
+            float m = 3.0e38f; uint32_t bs = 1;
+            #pragma unroll
+            for (int a = 1; a < j; a++) { const float v = cl[a] + cr[j - a]; if (v < m) { m = v; bs = (uint32_t)a; } }
+            open[j] = m; splits |= bs << (3 * (j - 2));
+        }
+        float c[9]; uint32_t choices = 0, ch = 1;
+        c[1] = half_area(B.bvh[p]) + open[8];
+        #pragma unroll
+        for (int k = 2; k <= 8; k++) {
+            c[k] = c[k - 1];
+            if (open[k] < c[k]) { c[k] = open[k]; ch = (uint32_t)k; }
+            choices |= ch << (4 * (k - 2));
+        }
+        cost4[2 * (size_t)p] = make_float4(c[1], c[2], c[3], c[4]);
+        cost4[2 * (size_t)p + 1] = make_float4(c[5], c[6], c[7], c[8]);
+        B.plan[p] = make_uint2(choices, splits);
+        cur = p;
+    }
+}
+
 __global__ void k_wide_prep(BuildCtx B, int parity) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         B.counters[3 - parity] = 0;
@@ -54,6 +128,28 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
 
         // ---- 1. choose up to 8 children by expanding the largest box first ----
         int ch[8]; int n = 1; ch[0] = root;
+        if (B.use_plan && !is_leaf(B, root)) {
+            // the planned cut: the root is opened over all 8 slots, every other node follows its own choice
+            int st_node[8], st_k[8]; int sp = 0;
+            n = 0;
+            st_node[0] = root; st_k[0] = 8; sp = 1;
+            bool first = true;
+            while (sp > 0 && n < 8) {
+                sp--;
+                const int node = st_node[sp], k = st_k[sp];
+                if (is_leaf(B, node)) { ch[n++] = node; first = false; continue; }
+                const uint2 pl = B.plan[node];
+                const uint32_t j = first ? 8u : (k >= 2 ? ((pl.x >> (4 * (k - 2))) & 15u) : 1u);
+                first = false;
+                if (j < 2u || j > (uint32_t)k) { ch[n++] = node; continue; }       // stays one inner child
+                uint32_t a = (pl.y >> (3 * (j - 2u))) & 7u;
+                if (a < 1u) a = 1u;
+                if (a > j - 1u) a = j - 1u;
+                if (sp + 2 > 8) { ch[n++] = node; continue; }
+                st_node[sp] = (int)B.bvh[node].right_offset; st_k[sp] = (int)(j - a); sp++;
+                st_node[sp] = node + 1; st_k[sp] = (int)a; sp++;
+            }
+        } else
         // phase 0 expands anything bigger than a leaf child; phase 1 then splits leaf children
         // further while slots remain (a box test is cheaper than a triangle test)
         for (int phase = 0; phase < 2; phase++) {
@@ -170,7 +266,9 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
     }
 }
 
-size_t wide_scratch_bytes(uint32_t max_nodes) { return 64 + 2 * (size_t)(max_nodes + 16) * sizeof(uint2); }
+// queues + the collapse plan's arrays for up to 2 * max_nodes binary nodes (max_nodes >= n_bvh / 2 + 16)
+static size_t plan_offset(uint32_t max_nodes) { return (64 + 2 * (size_t)(max_nodes + 16) * sizeof(uint2) + 255) & ~(size_t)255; }
+size_t wide_scratch_bytes(uint32_t max_nodes) { return plan_offset(max_nodes) + 2 * (size_t)max_nodes * (32 + 8 + 4 + 4) + 1024; }
 
 void launch_wide_build(const BvhNode* bvh, int n_bvh, const Triangle* tris, int n_tris, uint4* out_nodes,
                        float4* out_tris, uint32_t max_nodes, uint32_t* d_scratch, cudaStream_t stream) {
@@ -180,6 +278,23 @@ void launch_wide_build(const BvhNode* bvh, int n_bvh, const Triangle* tris, int 
     B.counters = d_scratch;
     B.queue[0] = reinterpret_cast<uint2*>(d_scratch + 16);
     B.queue[1] = B.queue[0] + (max_nodes + 16);
+    // WGPT_COLLAPSE=greedy keeps the largest-area-first expansion (for A/B measurements)
+    const char* how = getenv("WGPT_COLLAPSE");
+    B.use_plan = !(how && how[0] == 'g') && n_bvh >= 3 && (size_t)n_bvh <= 2 * (size_t)max_nodes;
+    {
+        char* p = reinterpret_cast<char*>(d_scratch) + plan_offset(max_nodes);
+        const size_t cap = 2 * (size_t)max_nodes;
+        B.cost = reinterpret_cast<float*>(p); p += cap * 32;
+        B.plan = reinterpret_cast<uint2*>(p); p += cap * 8;
+        B.parent = reinterpret_cast<int*>(p); p += cap * 4;
+        B.arrived = reinterpret_cast<uint32_t*>(p);
+    }
+    if (B.use_plan) {
+        cudaMemsetAsync(B.arrived, 0, (size_t)n_bvh * 4, stream);
+        const unsigned blocks = (unsigned)((n_bvh + 255) / 256);
+        k_plan_parents<<<blocks, 256, 0, stream>>>(B);
+        k_plan_costs<<<blocks, 256, 0, stream>>>(B);
+    }
     k_wide_init<<<1, 32, 0, stream>>>(B);
     // a wide level consumes >= 1 binary level, and stack_size <= 64 bounds the useful depth
     for (int level = 0; level < 48; level++) {
