@@ -46,6 +46,7 @@ DeviceScene make_device_scene(wgpt_ctx* c, uint32_t pixel_limit) {
     DeviceScene S;
     memset(&S, 0, sizeof(S));
     S.uniforms = c->uniforms;
+    { volatile float w = c->uniforms.screenW, h = c->uniforms.screenH; S.aspect = w / h; }      // one IEEE binary32 division (SSE divss)
     S.K.NUM_SAMPLES = c->cfg.num_samples; S.K.MAX_BOUNCES = c->cfg.max_bounces; S.K.STRATIFY = c->cfg.stratify;
     S.K.IMPORTANCE_SAMPLING = c->cfg.importance_sampling; S.K.STACK_SIZE = c->cfg.stack_size;
     S.shard.tile_rank = c->cfg.tile_rank; S.shard.tile_world = c->cfg.tile_world; S.shard.tile_rows = c->cfg.tile_rows;

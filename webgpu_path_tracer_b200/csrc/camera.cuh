@@ -30,7 +30,7 @@ __device__ __forceinline__ uint32_t pixel_seed(uint32_t pixelIndex, float frameN
 __device__ __forceinline__ Ray camera_ray(const DeviceScene& S, v3 cam_origin, float s, float t) {
     const v4 d = mul4(S.uniforms.viewMatrix, V3(s, t, -1.7320508075688774f), 0.0f);
     const float l = fsq(fa(fa(fa(fm(d.x, d.x), fm(d.y, d.y)), fm(d.z, d.z)), fm(d.w, d.w)));
-    Ray r; r.o = cam_origin; r.d = V3(fd(d.x, l), fd(d.y, l), fd(d.z, l));
+    Ray r; r.o = cam_origin; r.d = V3(d.x, d.y, d.z) / l;      // three IEEE quotients by one divisor (pvec.cuh operator/)
     return r;
 }
 
@@ -38,7 +38,7 @@ __device__ __forceinline__ Ray camera_ray(const DeviceScene& S, v3 cam_origin, f
 // Stratified (shootRay.wgsl:11-30): cell (si, sj) of a sqrt_spp x sqrt_spp grid.
 __device__ __forceinline__ Ray sample_ray(const DeviceScene& S, const PixelSetup& p, int si, int sj, uint32_t& rng) {
     const float W = S.uniforms.screenW, H = S.uniforms.screenH;
-    const float aspect = fd(W, H);
+    const float aspect = S.aspect;                              // fd(W, H), invocation-invariant: divided once on the host
     float ox, oy;
     if (S.K.STRATIFY) {
         const float sqrt_spp = (float)sqrt((double)S.K.NUM_SAMPLES);

@@ -35,6 +35,7 @@ struct Shard {
 
 struct DeviceScene {
     Uniforms uniforms;
+    float aspect;                   // screenW / screenH as one IEEE f32 division (shootRay.wgsl:36), set with the uniforms
     Consts K;
     Shard shard;
     int W, H;

@@ -427,7 +427,9 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
                 gen = true; gen_pixel = pixel;                             // next sample, same RNG stream
             } else {
                 const float div = S.K.STRATIFY ? pix.w : (float)S.K.NUM_SAMPLES;
-                P.stage[(size_t)ring_slot * npix + pixel] = make_float4(fd(pix.x, div), fd(pix.y, div), fd(pix.z, div), 1.0f);
+                // x / 1 is x (HEAD has NUM_SAMPLES = 1): no need to run three IEEE divisions for it
+                const v3 mean = div == 1.0f ? V3(pix.x, pix.y, pix.z) : V3(pix.x, pix.y, pix.z) / div;
+                P.stage[(size_t)ring_slot * npix + pixel] = make_float4(mean.x, mean.y, mean.z, 1.0f);
                 atomicAdd(&s_done[ring_slot], 1u);
                 need_work = true;
             }
