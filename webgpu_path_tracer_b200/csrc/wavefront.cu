@@ -211,8 +211,9 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                 }
             }
             // ---- triangle phase: one parked triangle per lane, once enough lanes have one ----
-            const int n_tri = __popc(__ballot_sync(0xffffffffu, has && (pk & 0xffu) != 0u));
-            const int n_node = __popc(__ballot_sync(0xffffffffu, has && tm == 0u && ((G.y & 0xff000000u) || sp > 0)));
+            const uint32_t m_tri = __ballot_sync(0xffffffffu, has && (pk & 0xffu) != 0u);
+            const uint32_t m_node = __ballot_sync(0xffffffffu, has && tm == 0u && ((G.y & 0xff000000u) || sp > 0));
+            const int n_tri = __popc(m_tri), n_node = __popc(m_node);
                         if (n_tri >= WF_TRI_BATCH || (n_tri > 0 && n_tri * WF_TRI_ADAPT >= n_node)) {
                 if (has && (pk & 0xffu) != 0u) {
                     const int b = __ffs((int)pk) - 1;
@@ -234,7 +235,10 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
             }
             // a lane whose walk is over idles until the warp refills; its result is written back then, together
             // with the other finished lanes (done one by one as each lane finished, that code ran 2 lanes wide)
-            const int active = __popc(__ballot_sync(0xffffffffu, has && (tm != 0u || (pk & 0xffu) != 0u || (G.y & 0xff000000u) || sp > 0)));
+            // lanes with work left, as of BEFORE the triangle phase (a lane blocked on tm != 0 also has a parked set, so the
+            // two masks cover it): the triangle phase only removes work, so this never undercounts; at worst the warp runs
+            // one empty pass before it refills, which is cheaper than a third vote in every pass
+            const int active = __popc(m_tri | m_node);
             if (active == 0) break;
             if (!exhausted && active < WF_REFILL_BELOW) break;
         }
