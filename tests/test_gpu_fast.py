@@ -114,6 +114,31 @@ def test_wide_traversal_equals_reference_walk_on_random_rays(golden_meshes):
     assert np.array_equal(tb, tg[:20000]) and np.array_equal(ib, ig[:20000]) and np.array_equal(bits(db), bits(dg[:20000]))
 
 
+@pytest.mark.parametrize("tree", ["device", "reference"])
+def test_collapse_plan_and_greedy_collapse_give_the_same_hits(golden_meshes, monkeypatch, tree):
+    """K2's SAH-optimal collapse plan (default) and the largest-area-first expansion (WGPT_COLLAPSE=greedy) are two
+    shapes of the same superset search: identical closest hits on random rays, every triangle in exactly one leaf slot."""
+    data = {"vertices": golden_meshes["monkey_smooth_15744_vertices"], "normals": golden_meshes["monkey_smooth_15744_normals"]}
+    scene, cam = scenes.mesh_in_room(data, scenes.DRAGON_MAT, [("scale", 0.7, 0.7, 0.7), ("translate", 0.0, -0.2, 0)])
+    rays, seeds = scenes.random_rays(500_000, 11)
+    monkeypatch.setenv("WGPT_BVH", tree)
+    out = {}
+    for how in ("greedy", "plan"):
+        monkeypatch.setenv("WGPT_COLLAPSE", how)
+        g = PathTracer(8, 8, mode=MODE_FAST)
+        g.write_scene(scene.buffers())
+        out[how] = g.trace_rays(rays, seeds) + (g.fast_statistics(),)
+        g.close()
+    e = PathTracer(8, 8, mode=MODE_EXACT)
+    e.write_scene(scene.buffers())
+    te, ie, de = e.trace_rays(rays, seeds)
+    for how in ("greedy", "plan"):
+        t, i, d, st = out[how]
+        assert np.array_equal(t, te) and np.array_equal(i, ie) and np.array_equal(bits(d), bits(de))
+        assert st["wide_tris"] == 15744
+        assert 15744 // 8 < st["wide_nodes"] < 15744
+
+
 def test_coplanar_ties_resolve_like_the_reference_walk():
     """The atrium stand-in is full of coplanar, overlapping faces (column caps on the floor and under the
     lintels): rays hit two triangles at exactly the same distance and the reference keeps the one it visits

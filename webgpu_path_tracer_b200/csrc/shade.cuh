@@ -27,16 +27,17 @@ __device__ __forceinline__ TriNormals load_tri_normals(const DeviceScene& S, int
 }
 
 // What hit_sphere / hit_volume / hit_quad / hit_triangle store into hitRec on accept
-// (common.wgsl:54-71, 140-143, 176-185, 224-239), computed once for the closest hit.
+// (common.wgsl:54-71, 140-143, 176-185, 224-239), computed once for the closest hit.  SPH = false: no spheres exist.
+template <bool SPH = true>
 __device__ __forceinline__ void finalize_hit(const DeviceScene& S, const Ray& ray, const HitLite& h,
                                              const TriNormals& tn, ShadeState& st) {
     st.p = at(ray, h.t);
-    if (h.kind == HIT_SPHERE) {
+    if (SPH && h.kind == HIT_SPHERE) {
         const Sphere s = S.spheres[h.index];
         st.n = normalize((st.p - V3(s.cx, s.cy, s.cz)) / s.r);
         st.front_face = dot(ray.d, st.n) < 0.0f;
         if (!st.front_face) st.n = -st.n;
-    } else if (h.kind == HIT_VOLUME) {
+    } else if (SPH && h.kind == HIT_VOLUME) {
         const Sphere s = S.spheres[h.index];
         st.n = normalize(st.p - V3(s.cx, s.cy, s.cz));
         st.front_face = true;
@@ -173,7 +174,9 @@ __device__ __forceinline__ Ray material_scatter(const Material& m, const Ray& ra
 // One iteration of the bounce loop AFTER a hit (traceRay.wgsl:18-79): emission, scatter,
 // mixture-pdf weighting, Russian roulette.  Returns false when the path ends here.
 // `early_return` is set when traceRay.wgsl:51-53 fires (the path's radiance is REPLACED by
-// emission * throughput).
+// emission * throughput).  IS: -1 = header.wgsl:12 IMPORTANCE_SAMPLING read at run time, 0 / 1 = known to the caller
+// (the other branch is not compiled in).
+template <int IS = -1>
 __device__ __forceinline__ bool bounce_update(const DeviceScene& S, const Material& m, int i, Ray& ray,
                                               ShadeState& st, uint32_t& rng, unsigned& draws,
                                               v3& acc_radiance, v3& throughput, bool& early_return) {
@@ -181,7 +184,8 @@ __device__ __forceinline__ bool bounce_update(const DeviceScene& S, const Materi
     v3 emission = ld3(m.emissionColor);
     if (!st.front_face) emission = V3s(0.0f);
 
-    if (S.K.IMPORTANCE_SAMPLING) {
+    const bool importance_sampling = IS < 0 ? S.K.IMPORTANCE_SAMPLING != 0 : IS != 0;
+    if (importance_sampling) {
         const Ray scattered_surface = material_scatter(m, ray, st, rng, draws);
         if (st.skip_pdf) {
             acc_radiance = acc_radiance + emission * throughput;

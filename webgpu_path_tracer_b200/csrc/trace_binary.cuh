@@ -10,12 +10,15 @@ namespace wg {
 
 #define WGPT_MAX_STACK 64
 
-// spheres + quads part (hitRay.wgsl:6-40), shared by both traversals
+// spheres + quads part (hitRay.wgsl:6-40), shared by both traversals.  SPH = false: the caller knows the scene has
+// no spheres (binding 1 empty) and the sphere / volume code is not even compiled in.
+template <bool SPH = true>
 __device__ __forceinline__ bool hit_analytic(const DeviceScene& S, const Ray& ray, uint32_t& rng,
                                              Counts* cnt, float& closest, HitLite& h) {
     bool hit_anything = false;
     unsigned draws = 0;
-    for (int i = 0; i < S.NUM_SPHERES; i++) {
+    const int n_spheres = SPH ? S.NUM_SPHERES : 0;
+    for (int i = 0; i < n_spheres; i++) {
         const Sphere s = S.spheres[i];
         const float medium = __ldg(&S.materials[(int)s.material_id].material_type);
         if (medium < 3.0f) {

@@ -289,8 +289,13 @@ __device__ __forceinline__ void start_sample(const DeviceScene& S, uint32_t pixe
 #ifndef WF_SHADE_MINB
 #define WF_SHADE_MINB 4
 #endif
-template <bool COUNT>
+// SPEC: what the launcher knows about the scene, so that code the scene cannot reach is not in the kernel at all
+// (the generic kernel is 170 KB of instructions; 9 % of its issue stalls were instruction fetches): -1 = nothing
+// (everything decided at run time), else bit 0 = binding 1 holds spheres, bit 1 = IMPORTANCE_SAMPLING is on.
+template <bool COUNT, int SPEC>
 __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(DeviceScene S, WfParams P) {
+    constexpr bool SPH = SPEC < 0 || (SPEC & 1) != 0;
+    constexpr int IS = SPEC < 0 ? -1 : ((SPEC >> 1) & 1);
     __shared__ uint32_t s_done[WF_MAX_RING];
     __shared__ uint32_t s_key_cnt[32];                 // slots per shade key
     __shared__ float4 s_x[WF_SHADE_THREADS];            // (tag, hit index, u, v) of the block's slots
@@ -413,10 +418,10 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
             st.p = st.n = st.unit_w = st.u = st.v = V3s(0.0f);
             st.front_face = false; st.skip_pdf = false; st.doSpecular = 0.0f;
             st.skip_ray.o = st.skip_ray.d = V3s(0.0f);
-            finalize_hit(S, ray, h, tn, st);
+            finalize_hit<SPH>(S, ray, h, tn, st);
             const Material m = S.materials[h.mat_id];
             bool early;
-            const bool cont = bounce_update(S, m, (int)bounce, ray, st, rng, n_draws, acc, thr, early);
+            const bool cont = bounce_update<IS>(S, m, (int)bounce, ray, st, rng, n_draws, acc, thr, early);
             bounce++;
             ended = !cont || (int)bounce >= S.K.MAX_BOUNCES;           // `for (i < MAX_BOUNCES)`
             alive = !ended;
@@ -503,7 +508,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         HitLite h; h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1;
         float closest = WGPT_MAX_FLOAT;
         if (COUNT) cnt.rays++;
-        const bool hit_a = hit_analytic(S, ray, rng, COUNT ? &cnt : nullptr, closest, h);
+        const bool hit_a = hit_analytic<SPH>(S, ray, rng, COUNT ? &cnt : nullptr, closest, h);
         trace = S.NUM_AABB > 0 && root_box_hit(S, ray, closest);
         const int ncls = trace ? WF_CLS_TRACE : (hit_a ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS);
         const uint32_t ctr = wf_ctr(ring_slot, bounce, scnt);
@@ -603,8 +608,13 @@ void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     if (ev) cudaEventRecord(ev[1], stream);
     const unsigned shade_blocks = (P.pool.capacity + WF_SHADE_THREADS - 1u) / WF_SHADE_THREADS;
-    if (S.counters) k_wf_shade<true><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P);
-    else k_wf_shade<false><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P);
+    if (S.counters) k_wf_shade<true, -1><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P);
+    else switch ((S.NUM_SPHERES > 0 ? 1 : 0) | (S.K.IMPORTANCE_SAMPLING ? 2 : 0)) {
+        case 0: k_wf_shade<false, 0><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P); break;
+        case 1: k_wf_shade<false, 1><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P); break;
+        case 2: k_wf_shade<false, 2><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P); break;
+        default: k_wf_shade<false, 3><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P); break;
+    }
     if (ev) cudaEventRecord(ev[2], stream);
     k_wf_ctl_end<<<1, 32, 0, stream>>>(P);
     const uint32_t npix = (uint32_t)S.W * (uint32_t)S.H;
