@@ -323,7 +323,9 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         const uint32_t key = cls0 < WF_CLS_MISS ? (uint32_t)(cls0 * 4 + (kind0 & 3)) : (uint32_t)(12 + cls0);
         const uint32_t peers = __match_any_sync(0xffffffffu, key);
         const int leader = __ffs((int)peers) - 1;
-        __syncthreads();
+        // (the barrier the sort needs anyway) a block whose slots are all dead has nothing to shade, start or publish:
+        // the last iterations of a render launch 32 K such blocks each
+        if (!__syncthreads_or(cls0 != WF_CLS_DEAD)) return;
         uint32_t warp_base = 0;
         if ((int)lane == leader) warp_base = atomicAdd(&s_key_cnt[key], (uint32_t)__popc(peers));
         warp_base = __shfl_sync(0xffffffffu, warp_base, leader);
