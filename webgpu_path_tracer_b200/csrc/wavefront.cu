@@ -25,6 +25,9 @@
 
 namespace wg {
 
+#ifndef WF_SPARSE_BELOW
+#define WF_SPARSE_BELOW 4        // shade runs over the live list once it holds fewer than capacity / this many slots
+#endif
 #ifndef WF_REFILL_BELOW
 #define WF_REFILL_BELOW 22      // refill the warp when fewer lanes than this still traverse (finished lanes write back together then)
 #endif
@@ -44,6 +47,7 @@ __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
         for (int k = 0; k < WF_MAX_RING; k++) c->done[k] = 0;
         c->acc_k = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
         c->finished = n_frames == 0 ? 1u : 0u; c->fallbacks = 0; c->iterations = 0;
+        c->drain = 0; c->sparse = 0; c->live_read = 0; c->n_live = 0; c->n_live_next = 0;
     }
 }
 
@@ -271,6 +275,11 @@ __global__ void k_wf_ctl_end(WfParams P) {
     unsigned long long lim = (unsigned long long)(c->acc_k + P.ring) * P.items_per_frame;
     c->work_limit = lim < c->total_work ? lim : c->total_work;
     if (c->acc_k == c->n_frames) c->finished = 1;
+    // drain bookkeeping: the shade launch that just ran listed its live slots iff it saw drain == 1
+    c->n_live = c->n_live_next; c->n_live_next = 0;
+    if (c->drain) c->live_read ^= 1u;
+    c->sparse = (c->drain && (unsigned long long)c->n_live * WF_SPARSE_BELOW <= P.pool.capacity) ? 1u : 0u;
+    if (c->next_work >= c->total_work) c->drain = 1;
     c->iterations++;
 }
 
@@ -301,12 +310,20 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     __shared__ float4 s_x[WF_SHADE_THREADS];            // (tag, hit index, u, v) of the block's slots
     __shared__ uint32_t s_perm[WF_SHADE_THREADS];
     __shared__ uint32_t s_q[WF_SHADE_THREADS];          // slot ids for the next ray queue
-    __shared__ uint32_t s_qn, s_arrived;
+    __shared__ uint32_t s_slot[WF_SHADE_THREADS];       // sparse launches: the slot of list entry (block base + i)
+    __shared__ uint32_t s_live[WF_SHADE_THREADS];       // drain phase: slot ids for the next live list
+    __shared__ uint32_t s_qn, s_arrived, s_ln;
     WfControl* ctl = P.ctl;
     if (ctl->finished) return;                             // the host notices the flag one batch late: those launches are empty
+    // drain phase (WfControl): list the slots that stay alive; sparse launch: shade the previous list, not every slot
+    const bool drain = ctl->drain != 0u, sparse = ctl->sparse != 0u;
+    const uint32_t n_live = ctl->n_live;
+    const uint32_t* __restrict__ live_in = P.q_live[ctl->live_read & 1u];
+    uint32_t* __restrict__ live_out = P.q_live[(ctl->live_read & 1u) ^ 1u];
+    if (sparse && blockIdx.x * blockDim.x >= n_live) return;
     const uint32_t lane = threadIdx.x & 31u;
     for (uint32_t k = threadIdx.x; k < WF_MAX_RING; k += blockDim.x) s_done[k] = 0;
-    if (threadIdx.x == 0) { s_qn = 0; s_arrived = 0; }
+    if (threadIdx.x == 0) { s_qn = 0; s_arrived = 0; s_ln = 0; }
 
     // ---- material sort inside the block: slot (block base + j) -> thread rank by shade key ----
     // key = (material class, hit kind) for hits, then miss / idle / dead / trace: warps end up
@@ -315,7 +332,8 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     const uint32_t block_base = blockIdx.x * blockDim.x;
     if (threadIdx.x < 32) s_key_cnt[threadIdx.x] = 0;
     {
-        const uint32_t s0 = block_base + threadIdx.x;
+        uint32_t s0 = block_base + threadIdx.x;
+        if (sparse) { s0 = s0 < n_live ? live_in[s0] : 0xffffffffu; s_slot[threadIdx.x] = s0; }
         float4 xv0 = make_float4(__uint_as_float(wf_tag(HIT_NONE, WF_CLS_DEAD, -1)), 0.0f, 0.0f, 0.0f);
         if (s0 < P.pool.capacity) xv0 = P.pool.x[s0];
         s_x[threadIdx.x] = xv0;
@@ -340,7 +358,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         __syncthreads();
     }
     const uint32_t j = s_perm[threadIdx.x];
-    const uint32_t slot = block_base + j;
+    const uint32_t slot = sparse ? s_slot[j] : block_base + j;
     const float4 xv = s_x[j];
     // (hit kind, hit index, material id, shade class) of the slot
     int4 hid = make_int4(wf_tag_kind(__float_as_uint(xv.x)), __float_as_int(xv.y), wf_tag_mat(__float_as_uint(xv.x)), wf_tag_cls(__float_as_uint(xv.x)));
@@ -537,6 +555,15 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
             wbase = __shfl_sync(0xffffffffu, wbase, 0);
             if (trace) s_q[wbase + (uint32_t)__popc(m & lanemask_lt())] = slot;
         }
+        if (drain) {
+            const uint32_t ml = __ballot_sync(0xffffffffu, alive);
+            if (ml) {
+                uint32_t lbase = 0;
+                if (lane == 0) lbase = atomicAdd(&s_ln, (uint32_t)__popc(ml));
+                lbase = __shfl_sync(0xffffffffu, lbase, 0);
+                if (alive) s_live[lbase + (uint32_t)__popc(ml & lanemask_lt())] = slot;
+            }
+        }
         __syncwarp();
         uint32_t last = 0;
         if (lane == 0) { __threadfence_block(); last = atomicAdd(&s_arrived, 1u) == WF_SHADE_THREADS / 32 - 1 ? 1u : 0u; }
@@ -548,6 +575,13 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
             if (lane == 0 && total) base = atomicAdd(&ctl->n_next, total);
             base = __shfl_sync(0xffffffffu, base, 0);
             for (uint32_t i = lane; i < total; i += 32) P.q_extend[base + i] = ((volatile uint32_t*)s_q)[i];
+            if (drain) {
+                const uint32_t nl = *(volatile uint32_t*)&s_ln;
+                uint32_t lb = 0;
+                if (lane == 0 && nl) lb = atomicAdd(&ctl->n_live_next, nl);
+                lb = __shfl_sync(0xffffffffu, lb, 0);
+                for (uint32_t i = lane; i < nl; i += 32) live_out[lb + i] = ((volatile uint32_t*)s_live)[i];
+            }
             for (uint32_t k = lane; k < P.ring; k += 32) {
                 const uint32_t v = ((volatile uint32_t*)s_done)[k];
                 if (v) atomicAdd(&ctl->done[k], v);

@@ -40,7 +40,7 @@ struct PathPool {
     float4* pix;     // pixColor of the (pixel, frame) so far .xyz, .w = samples taken (stratified divisor)
     uint32_t capacity;
 };
-#define WF_BYTES_PER_SLOT (6 * 16 + 4)      /* 6 records + one ray-queue entry */
+#define WF_BYTES_PER_SLOT (6 * 16 + 4 + 8)  /* 6 records + one ray-queue entry + two live-list entries */
 #define WF_MAX_BOUNCE_FIELD 1023
 #define WF_MAX_SAMPLE_FIELD 16383
 #define WF_CTR_FIRST_QUERY_MASK 0x00ffffffu   /* bounce == 0 and sample == 0: the primary ray of the item */
@@ -65,12 +65,20 @@ struct WfControl {
     uint32_t finished;
     uint32_t fallbacks;                // rays re-traced with the reference-order walk
     uint32_t iterations;
+    // Drain: once every work item has been handed out no slot can start a new path, and the live slots thin out
+    // over many iterations (a few long paths keep a render going).  Shade then lists the slots that are still
+    // alive, and once that list is short the next shade launches run over the LIST instead of over every slot.
+    uint32_t drain;                    // all work handed out (set by k_wf_ctl_end; shade lists its live slots from then on)
+    uint32_t sparse;                   // this iteration's shade runs over q_live[live_read][0 .. n_live)
+    uint32_t live_read;                // which of the two live lists is read (the other one is being written)
+    uint32_t n_live, n_live_next;
 };
 
 struct WfParams {
     PathPool pool;
     WfControl* ctl;
     uint32_t* q_extend;                // slot ids of live rays, compacted by shade (capacity entries)
+    uint32_t* q_live[2];               // slot ids of live paths (drain phase), double-buffered
     float4* stage;                     // ring x W*H: (pixColor, 1)
     uint32_t ring;                     // frames in flight
     uint32_t items_per_frame;          // shard.n_pixels
