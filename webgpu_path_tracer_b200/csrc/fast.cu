@@ -36,6 +36,7 @@ struct FastState {
     uint64_t prof_launches[4] = {0, 0, 0, 0};
     cudaEvent_t wide_ev[2] = {nullptr, nullptr};
     bool wide_timed = false;
+    int wide_launches = 0;              // kernels of the last K2 run
 };
 
 static const size_t PROF_QUADS = 2048;
@@ -111,9 +112,9 @@ static int ensure_wide(wgpt_ctx* c) {
             c->last_launches += BVH_BUILD_LAUNCHES;
             src = F->own_bvh;
         }
-        launch_wide_build(src, n_bvh, (const Triangle*)c->dbuf[5], n_tri, F->wide_nodes, F->wide_tris,
-                          F->wide_cap, F->wide_scratch, c->stream);
-        c->last_launches += 1 + 2 * 48;
+        F->wide_launches = launch_wide_build(src, n_bvh, (const Triangle*)c->dbuf[5], n_tri, F->wide_nodes, F->wide_tris,
+                                             F->wide_cap, F->wide_scratch, c->stream);
+        c->last_launches += F->wide_launches;
         F->wstats = wide_build_stats(F->wide_scratch, c->stream);
         if ((e = cudaGetLastError()) != cudaSuccess) return cuda_err(c, e, "wide bvh build");
         F->own_used = own;
@@ -274,7 +275,7 @@ int fast_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]) {
         float t = 0;
         cudaEventSynchronize(F->wide_ev[1]);
         cudaEventElapsedTime(&t, F->wide_ev[0], F->wide_ev[1]);
-        F->prof_ms[3] += t; F->prof_launches[3] += 1 + 2 * 48 + (F->own_used ? BVH_BUILD_LAUNCHES : 0); F->wide_timed = false;
+        F->prof_ms[3] += t; F->prof_launches[3] += F->wide_launches + (F->own_used ? BVH_BUILD_LAUNCHES : 0); F->wide_timed = false;
     }
     for (int i = 0; i < 4; i++) { ms[i] = (float)F->prof_ms[i]; launches[i] = F->prof_launches[i]; F->prof_ms[i] = 0; F->prof_launches[i] = 0; }
     return WGPT_OK;

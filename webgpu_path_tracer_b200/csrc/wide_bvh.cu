@@ -270,8 +270,8 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
 static size_t plan_offset(uint32_t max_nodes) { return (64 + 2 * (size_t)(max_nodes + 16) * sizeof(uint2) + 255) & ~(size_t)255; }
 size_t wide_scratch_bytes(uint32_t max_nodes) { return plan_offset(max_nodes) + 2 * (size_t)max_nodes * (32 + 8 + 4 + 4) + 1024; }
 
-void launch_wide_build(const BvhNode* bvh, int n_bvh, const Triangle* tris, int n_tris, uint4* out_nodes,
-                       float4* out_tris, uint32_t max_nodes, uint32_t* d_scratch, cudaStream_t stream) {
+int launch_wide_build(const BvhNode* bvh, int n_bvh, const Triangle* tris, int n_tris, uint4* out_nodes,
+                      float4* out_tris, uint32_t max_nodes, uint32_t* d_scratch, cudaStream_t stream) {
     BuildCtx B;
     B.bvh = bvh; B.n_bvh = n_bvh; B.tris = tris; B.n_tris = n_tris;
     B.out_nodes = out_nodes; B.out_tris = out_tris; B.max_nodes = max_nodes;
@@ -302,6 +302,7 @@ void launch_wide_build(const BvhNode* bvh, int n_bvh, const Triangle* tris, int 
         k_wide_prep<<<1, 32, 0, stream>>>(B, parity);
         k_wide_level<<<148 * 4, 128, 0, stream>>>(B, parity);
     }
+    return 1 + 2 * 48 + (B.use_plan ? 2 : 0);
 }
 
 WideBuildStats wide_build_stats(const uint32_t* d_scratch, cudaStream_t stream) {

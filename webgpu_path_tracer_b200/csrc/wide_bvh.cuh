@@ -42,9 +42,10 @@ struct WideBuildStats { uint32_t n_nodes, n_tris, n_levels, overflow; };
 
 // K2 host entry (wide_bvh.cu): builds into caller-provided device storage of capacity
 // max_nodes (>= max(1, NUM_AABB/2)) nodes and NUM_TRIANGLES packed triangles.
-// d_scratch: >= 4 * (max_nodes + 16) uint32 of work-queue space + 16 counters.
+// d_scratch: wide_scratch_bytes(max_nodes) bytes (counters, two work queues, the collapse plan of up to 2 * max_nodes binary nodes).
 size_t wide_scratch_bytes(uint32_t max_nodes);
-void launch_wide_build(const BvhNode* bvh, int n_bvh, const Triangle* tris, int n_tris, uint4* out_nodes,
+// returns the number of kernels it launched
+int launch_wide_build(const BvhNode* bvh, int n_bvh, const Triangle* tris, int n_tris, uint4* out_nodes,
                        float4* out_tris, uint32_t max_nodes, uint32_t* d_scratch, cudaStream_t stream);
 // reads the counters back (synchronises the stream)
 WideBuildStats wide_build_stats(const uint32_t* d_scratch, cudaStream_t stream);
