@@ -47,7 +47,7 @@ __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
         for (int k = 0; k < WF_MAX_RING; k++) c->done[k] = 0;
         c->acc_k = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
         c->finished = n_frames == 0 ? 1u : 0u; c->fallbacks = 0; c->iterations = 0;
-        c->drain = 0; c->sparse = 0; c->live_read = 0; c->n_live = 0; c->n_live_next = 0;
+        c->drain = 0; c->sparse = 0; c->live_read = 0; c->n_live = 0; c->n_live_next = 0; c->n_tie_blocks = 0;
     }
 }
 
@@ -129,6 +129,13 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                 // A tie carries the closest distance along, an overflow of the wide stack does not.
                 if (!ambiguous) reinterpret_cast<float*>(&P.pool.x[slot])[2] = closest;
                 reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = (tag0 & ~0xf0u) | ((uint32_t)(ambiguous ? WF_CLS_OVERFLOW : WF_CLS_TIE) << 4);
+                {   // note the shade block of this slot (first marker of a block appends it to the front list)
+                    const uint32_t blk = slot / WF_SHADE_THREADS, bit = 1u << (blk & 31u);
+                    if (!(atomicOr(&P.tie_bitmap[blk >> 5], bit) & bit)) {
+                        const uint32_t at = atomicAdd(&ctl->n_tie_blocks, 1u);
+                        if (at < WF_FRONT_BLOCKS) P.tie_blocks[at] = blk;
+                    }
+                }
             } else {
                 const bool hit = hit_a | hit_t;
                 const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
@@ -261,8 +268,20 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
 
 // after shade: publish the next ray queue, find frames that completed, advance the ring window
 __global__ void k_wf_ctl_end(WfParams P) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (blockIdx.x != 0) return;
+    {   // the marks of this iteration have been consumed by the shade launch: clear them (one warp)
+        const uint32_t ntb = P.ctl->n_tie_blocks;
+        if (ntb <= WF_FRONT_BLOCKS) {
+            for (uint32_t i = threadIdx.x; i < ntb; i += blockDim.x) P.tie_bitmap[P.tie_blocks[i] >> 5] = 0u;
+        } else {
+            const uint32_t words = P.pool.capacity / WF_SHADE_THREADS / 32u + 1u;
+            for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) P.tie_bitmap[i] = 0u;
+        }
+        __syncwarp();
+    }
+    if (threadIdx.x != 0) return;
     WfControl* c = P.ctl;
+    c->n_tie_blocks = 0;
     c->n_extend = c->n_next; c->n_next = 0; c->extend_cursor = 0;
     uint32_t n_ready = 0;
     while (c->acc_k + n_ready < c->n_frames && n_ready < P.ring &&
@@ -292,9 +311,6 @@ __device__ __forceinline__ void start_sample(const DeviceScene& S, uint32_t pixe
     ray = sample_ray(S, ps, si, sj, rng);
 }
 
-#ifndef WF_SHADE_THREADS
-#define WF_SHADE_THREADS 256
-#endif
 #ifndef WF_SHADE_MINB
 #define WF_SHADE_MINB 4
 #endif
@@ -320,7 +336,21 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     const uint32_t n_live = ctl->n_live;
     const uint32_t* __restrict__ live_in = P.q_live[ctl->live_read & 1u];
     uint32_t* __restrict__ live_out = P.q_live[(ctl->live_read & 1u) ^ 1u];
-    if (sparse && blockIdx.x * blockDim.x >= n_live) return;
+    // which 256 slots (or list entries) this block takes: the leading WF_FRONT_BLOCKS blocks run the blocks that hold
+    // marked slots (wavefront.cuh, tie_bitmap), everyone else its natural position unless a leading block has it
+    uint32_t nat;
+    {
+        const uint32_t ntb = ctl->n_tie_blocks;
+        const bool front = !sparse && ntb > 0u && ntb <= WF_FRONT_BLOCKS;
+        if (blockIdx.x < WF_FRONT_BLOCKS) {
+            if (!front || blockIdx.x >= ntb) return;
+            nat = P.tie_blocks[blockIdx.x];
+        } else {
+            nat = blockIdx.x - WF_FRONT_BLOCKS;
+            if (front && ((P.tie_bitmap[nat >> 5] >> (nat & 31u)) & 1u)) return;
+        }
+    }
+    if (sparse && nat * blockDim.x >= n_live) return;
     const uint32_t lane = threadIdx.x & 31u;
     for (uint32_t k = threadIdx.x; k < WF_MAX_RING; k += blockDim.x) s_done[k] = 0;
     if (threadIdx.x == 0) { s_qn = 0; s_arrived = 0; s_ln = 0; }
@@ -329,7 +359,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
     // key = (material class, hit kind) for hits, then miss / idle / dead / trace: warps end up
     // shading one material AND one primitive type (finalize_hit differs per kind).  Counting sort
     // with warp-aggregated shared atomics; the order inside a key does not matter.
-    const uint32_t block_base = blockIdx.x * blockDim.x;
+    const uint32_t block_base = nat * blockDim.x;
     if (threadIdx.x < 32) s_key_cnt[threadIdx.x] = 0;
     {
         uint32_t s0 = block_base + threadIdx.x;
@@ -643,7 +673,7 @@ void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams
     if (S.counters) k_wf_extend<true><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     if (ev) cudaEventRecord(ev[1], stream);
-    const unsigned shade_blocks = (P.pool.capacity + WF_SHADE_THREADS - 1u) / WF_SHADE_THREADS;
+    const unsigned shade_blocks = (P.pool.capacity + WF_SHADE_THREADS - 1u) / WF_SHADE_THREADS + WF_FRONT_BLOCKS;
     if (S.counters) k_wf_shade<true, -1><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P);
     else switch ((S.NUM_SPHERES > 0 ? 1 : 0) | (S.K.IMPORTANCE_SAMPLING ? 2 : 0)) {
         case 0: k_wf_shade<false, 0><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P); break;

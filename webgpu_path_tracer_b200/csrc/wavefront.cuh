@@ -11,6 +11,12 @@
 namespace wg {
 
 #define WF_MAX_RING 256
+#ifndef WF_SHADE_THREADS
+#define WF_SHADE_THREADS 256     // slots per shade block
+#endif
+#ifndef WF_FRONT_BLOCKS
+#define WF_FRONT_BLOCKS 512      // leading shade blocks that take over the blocks holding marked slots
+#endif
 // slot status / shade class, kept in hid.w: 0..3 = material_type of the hit to shade, 4 = miss to
 // shade, 5 = idle (no path; waiting for the ring window to release work), 6 = dead (no path, no
 // work left), 7 = in the extend queue
@@ -72,6 +78,7 @@ struct WfControl {
     uint32_t sparse;                   // this iteration's shade runs over q_live[live_read][0 .. n_live)
     uint32_t live_read;                // which of the two live lists is read (the other one is being written)
     uint32_t n_live, n_live_next;
+    uint32_t n_tie_blocks;             // shade blocks that hold a slot the extend stage marked (tie / stack overflow) this iteration
 };
 
 struct WfParams {
@@ -79,6 +86,12 @@ struct WfParams {
     WfControl* ctl;
     uint32_t* q_extend;                // slot ids of live rays, compacted by shade (capacity entries)
     uint32_t* q_live[2];               // slot ids of live paths (drain phase), double-buffered
+    // The reference-order walk of a marked slot is one long chain of dependent loads (tens of microseconds); a shade
+    // launch cannot end before its slowest one.  The extend stage therefore notes WHICH shade blocks hold marked
+    // slots, and the shade launch runs exactly those blocks first (WF_FRONT_BLOCKS leading blocks take them, the
+    // block at the natural position leaves), so the walks overlap the rest of the launch instead of trailing it.
+    uint32_t* tie_bitmap;              // one bit per shade block (capacity / WF_SHADE_THREADS)
+    uint32_t* tie_blocks;              // WF_FRONT_BLOCKS entries
     float4* stage;                     // ring x W*H: (pixColor, 1)
     uint32_t ring;                     // frames in flight
     uint32_t items_per_frame;          // shard.n_pixels
