@@ -182,3 +182,23 @@ def test_png_and_ppm_writers_round_trip(tmp_path):
     imageio.write_ppm(p, img)
     raw = p.read_bytes()
     assert raw.startswith(b"P6\n53 37\n255\n") and raw[len(b"P6\n53 37\n255\n"):] == want[:, :, :3].tobytes()
+
+
+def test_napi_addon_source_passes_a_syntax_check_and_binds_only_declared_entry_points():
+    """N3: the Node addon is source only here (no node, no node_api.h).  It must at least be valid
+    C++ against the N-API signatures it uses (stand-in header under tests/napi_stub) and call nothing that
+    include/wgpt.h does not declare."""
+    import re, shutil, subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = os.path.join(root, "bindings", "napi", "addon.cc")
+    if shutil.which("g++"):
+        subprocess.check_call(["g++", "-std=c++17", "-fsyntax-only", "-Wall", "-Werror", "-I" + os.path.join(root, "tests", "napi_stub"),
+                               "-I" + os.path.join(root, "include"), src])
+    header = open(os.path.join(root, "include", "wgpt.h")).read()
+    used = set(re.findall(r"\b(wgpt_[a-z_0-9]+)\s*\(", open(src).read()))
+    assert used and all(re.search(r"\b%s\s*\(" % u, header) for u in used), used
+    shim = open(os.path.join(root, "bindings", "napi", "wgpt-utils.js")).read()
+    for method in ("createUniformBuffer", "createStorageBuffer_WriteOnly", "createStorageBuffer_ReadWrite", "createVertexBuffer",
+                   "createShaderModule", "createComputePipeline", "createRenderPipeline", "createRenderPassDescriptor",
+                   "computePass", "renderPass", "createBindGroup", "writeBuffer", "init"):
+        assert re.search(r"\b%s\s*\(" % method, shim), method        # the call shapes renderer.js uses
