@@ -149,7 +149,7 @@ static int ensure_pool(wgpt_ctx* c) {
     ring = std::max(2u, std::min<uint32_t>(ring, WF_MAX_RING));
     // one allocation, carved into 16-byte-aligned arrays
     const size_t per_slot = WF_BYTES_PER_SLOT;
-    const size_t bytes = (size_t)cap * per_slot + (size_t)ring * npix * 16 + (size_t)cap / WF_SHADE_THREADS / 8 + WF_FRONT_BLOCKS * 4 + 48 * 256;
+    const size_t bytes = (size_t)cap * per_slot + (size_t)ring * npix * 16 + (size_t)cap / WF_SHADE_THREADS / 8 + WF_FRONT_BLOCKS * 4 + WF_WORK_SHARDS * 128 + 56 * 256;
     cudaError_t e;
     if ((e = cudaMalloc(&F->pool_mem, bytes)) != cudaSuccess) return cuda_err(c, e, "wavefront pool alloc");
     if ((e = cudaMemsetAsync(F->pool_mem, 0, bytes, c->stream)) != cudaSuccess) return cuda_err(c, e, "wavefront pool clear");
@@ -164,6 +164,7 @@ static int ensure_pool(wgpt_ctx* c) {
     P.pool.capacity = cap;
     P.q_extend = (uint32_t*)carve((size_t)cap * 4);
     P.q_live[0] = (uint32_t*)carve((size_t)cap * 4); P.q_live[1] = (uint32_t*)carve((size_t)cap * 4);
+    P.work_shards = (unsigned long long*)carve((size_t)WF_WORK_SHARDS * 128);
     P.tie_bitmap = (uint32_t*)carve(((size_t)cap / WF_SHADE_THREADS / 32 + 2) * 4);
     P.tie_blocks = (uint32_t*)carve((size_t)WF_FRONT_BLOCKS * 4);
     P.stage = (float4*)carve((size_t)ring * npix * 16);

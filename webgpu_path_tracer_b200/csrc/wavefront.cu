@@ -43,6 +43,7 @@ __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
         c->total_work = (unsigned long long)n_frames * P.items_per_frame;
         const unsigned long long win = (unsigned long long)P.ring * P.items_per_frame;
         c->work_limit = win < c->total_work ? win : c->total_work;
+        for (uint32_t k = 0; k < WF_WORK_SHARDS; k++) { P.work_shards[16 * k] = 0ull; c->shard_lim[k] = wf_shard_count(c->work_limit, k); }
         c->n_extend = 0; c->extend_cursor = 0; c->n_next = 0;
         for (int k = 0; k < WF_MAX_RING; k++) c->done[k] = 0;
         c->acc_k = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
@@ -293,12 +294,17 @@ __global__ void k_wf_ctl_end(WfParams P) {
     c->acc_k += n_ready;
     unsigned long long lim = (unsigned long long)(c->acc_k + P.ring) * P.items_per_frame;
     c->work_limit = lim < c->total_work ? lim : c->total_work;
+    for (uint32_t k = 0; k < WF_WORK_SHARDS; k++) c->shard_lim[k] = wf_shard_count(c->work_limit, k);
     if (c->acc_k == c->n_frames) c->finished = 1;
     // drain bookkeeping: the shade launch that just ran listed its live slots iff it saw drain == 1
     c->n_live = c->n_live_next; c->n_live_next = 0;
     if (c->drain) c->live_read ^= 1u;
     c->sparse = (c->drain && (unsigned long long)c->n_live * WF_SPARSE_BELOW <= P.pool.capacity) ? 1u : 0u;
-    if (c->next_work >= c->total_work) c->drain = 1;
+    {   // all work handed out <=> every shard has dealt its last item
+        bool all = true;
+        for (uint32_t k = 0; k < WF_WORK_SHARDS; k++) all = all && P.work_shards[16 * k] >= wf_shard_count(c->total_work, k);
+        if (all) c->drain = 1;
+    }
     c->iterations++;
 }
 
@@ -351,6 +357,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         }
     }
     if (sparse && nat * blockDim.x >= n_live) return;
+    const uint32_t work_shard = nat % WF_WORK_SHARDS;
     const uint32_t lane = threadIdx.x & 31u;
     for (uint32_t k = threadIdx.x; k < WF_MAX_RING; k += blockDim.x) s_done[k] = 0;
     if (threadIdx.x == 0) { s_qn = 0; s_arrived = 0; s_ln = 0; }
@@ -502,25 +509,39 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         if (m) {
             const int leader = __ffs((int)m) - 1;
             const uint32_t want = (uint32_t)__popc(m);
-            unsigned long long old = 0; uint32_t granted = 0; int more_later = 0;
+            unsigned long long old = 0; uint32_t granted = 0, seg_shard = work_shard; int more_later = 0;
             if ((int)lane == leader) {
-                old = atomicAdd(&ctl->next_work, (unsigned long long)want);
-                const unsigned long long lim = ctl->work_limit;
-                granted = old >= lim ? 0u : (uint32_t)((lim - old) < want ? (lim - old) : want);
-                if (granted < want) atomicAdd(&ctl->next_work, (unsigned long long)0 - (unsigned long long)(want - granted));
-                more_later = lim < ctl->total_work;      // a later window advance can still release work
+                // the block's own shard first, then the others in turn (a pool with fewer blocks than shards, and the end
+                // of a window, leave items in foreign shards); a plain load tells whether a foreign shard has anything
+                // below its limit, so a starved warp does not pay 16 atomics.  One segment per claim: lanes beyond it
+                // stay idle and ask again in the next iteration.
+                for (uint32_t k = 0; k < WF_WORK_SHARDS && granted == 0u; k++) {
+                    const uint32_t c = (work_shard + k) % WF_WORK_SHARDS;
+                    unsigned long long* ctr = &P.work_shards[16u * c];
+                    const unsigned long long lim = ctl->shard_lim[c];
+                    if (k > 0u && *(volatile unsigned long long*)ctr >= lim) continue;
+                    const unsigned long long o = atomicAdd(ctr, (unsigned long long)want);
+                    const uint32_t g = o >= lim ? 0u : (uint32_t)((lim - o) < want ? (lim - o) : want);
+                    if (g < want) atomicAdd(ctr, (unsigned long long)0 - (unsigned long long)(want - g));
+                    if (g) { old = o; granted = g; seg_shard = c; }
+                }
+                // a lane left without an item waits (idle) if a later window advance can release work or if this claim
+                // stopped at its first segment; it is dead only when every shard was found empty at the end of the work
+                more_later = (granted != 0u || ctl->work_limit < ctl->total_work) ? 1 : 0;
             }
             old = __shfl_sync(0xffffffffu, old, leader);
             granted = __shfl_sync(0xffffffffu, granted, leader);
+            seg_shard = __shfl_sync(0xffffffffu, seg_shard, leader);
             more_later = __shfl_sync(0xffffffffu, more_later, leader);
             if (need_work) {
                 const uint32_t r = (uint32_t)__popc(m & lanemask_lt());
                 new_cls = more_later ? WF_CLS_IDLE : WF_CLS_DEAD;
                 if (r < granted) {
-                    // (frame ordinal, pixel) of item `old + r` without a 64-bit division: quotient
-                    // estimate in binary64 (exact to +-1 for old < 2^52), fixed up with integers
-                    uint32_t fk0 = (uint32_t)__double2ull_rz(__ull2double_rz(old) * P.inv_items_per_frame);
-                    long long rem = (long long)(old - (unsigned long long)fk0 * P.items_per_frame) + (long long)r;
+                    // (frame ordinal, pixel) of the shard's item `old + r` without a 64-bit division: quotient
+                    // estimate in binary64 (exact to +-1 for g < 2^52), fixed up with integers
+                    const unsigned long long g = wf_shard_item(old + r, seg_shard);
+                    uint32_t fk0 = (uint32_t)__double2ull_rz(__ull2double_rz(g) * P.inv_items_per_frame);
+                    long long rem = (long long)(g - (unsigned long long)fk0 * P.items_per_frame);
                     if (rem < 0) { fk0--; rem += P.items_per_frame; }
                     while (rem >= (long long)P.items_per_frame) { fk0++; rem -= P.items_per_frame; }
                     frame_k = fk0;

@@ -57,8 +57,27 @@ __host__ __device__ inline int wf_tag_cls(uint32_t tag) { return (int)((tag >> 4
 __host__ __device__ inline int wf_tag_mat(uint32_t tag) { return (int)(tag >> 8) == 0xffffff ? -1 : (int)(tag >> 8); }
 __host__ __device__ inline uint32_t wf_ctr(uint32_t ring_slot, uint32_t bounce, uint32_t scnt) { return (ring_slot << 24) | (bounce << 14) | (scnt & 0x3fffu); }
 
+// Work items (frame ordinal, pixel) are numbered g = 0 .. total_work - 1, frame-major.  One global counter handing them
+// out is a single L2 address taking an atomic from every shade warp of every launch (~0.5 per ns: its round trip was
+// 8-15 % of the shade stage's stall samples).  The item space is therefore dealt out in chunks of WF_WORK_CHUNK
+// consecutive items to WF_WORK_SHARDS counters, one cache line each (chunk q belongs to shard q % SHARDS); a shade block
+// claims from shard (block % SHARDS).  Inside a shard the local index l counts that shard's items in increasing g.
+#define WF_WORK_SHARDS 16
+#define WF_WORK_CHUNK_LOG2 8
+// number of items g < n that belong to shard c
+__host__ __device__ inline unsigned long long wf_shard_count(unsigned long long n, uint32_t c) {
+    const unsigned long long q = n >> WF_WORK_CHUNK_LOG2, r = n & ((1ull << WF_WORK_CHUNK_LOG2) - 1ull);
+    const unsigned long long full = q > c ? (q - c + WF_WORK_SHARDS - 1) / WF_WORK_SHARDS : 0ull;
+    return (full << WF_WORK_CHUNK_LOG2) + ((q % WF_WORK_SHARDS) == c ? r : 0ull);
+}
+// global item number of local index l of shard c
+__host__ __device__ inline unsigned long long wf_shard_item(unsigned long long l, uint32_t c) {
+    const unsigned long long q = (l >> WF_WORK_CHUNK_LOG2) * WF_WORK_SHARDS + c;
+    return (q << WF_WORK_CHUNK_LOG2) + (l & ((1ull << WF_WORK_CHUNK_LOG2) - 1ull));
+}
+
 struct WfControl {
-    unsigned long long next_work;      // next (frame ordinal, pixel) item to hand out
+    unsigned long long next_work;      // (unused since the counter is sharded: WfParams::work_shards)
     unsigned long long work_limit;     // items below this may start (ring window)
     unsigned long long total_work;
     uint32_t n_extend;                 // rays queued for the extend stage of this iteration
@@ -78,6 +97,7 @@ struct WfControl {
     uint32_t sparse;                   // this iteration's shade runs over q_live[live_read][0 .. n_live)
     uint32_t live_read;                // which of the two live lists is read (the other one is being written)
     uint32_t n_live, n_live_next;
+    unsigned long long shard_lim[WF_WORK_SHARDS];   // wf_shard_count(work_limit, c), refreshed with work_limit
     uint32_t n_tie_blocks;             // shade blocks that hold a slot the extend stage marked (tie / stack overflow) this iteration
 };
 
@@ -90,6 +110,7 @@ struct WfParams {
     // launch cannot end before its slowest one.  The extend stage therefore notes WHICH shade blocks hold marked
     // slots, and the shade launch runs exactly those blocks first (WF_FRONT_BLOCKS leading blocks take them, the
     // block at the natural position leaves), so the walks overlap the rest of the launch instead of trailing it.
+    unsigned long long* work_shards;   // WF_WORK_SHARDS counters, 16 words (128 B) apart: next local index of each shard
     uint32_t* tie_bitmap;              // one bit per shade block (capacity / WF_SHADE_THREADS)
     uint32_t* tie_blocks;              // WF_FRONT_BLOCKS entries
     float4* stage;                     // ring x W*H: (pixColor, 1)
