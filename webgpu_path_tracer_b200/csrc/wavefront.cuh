@@ -62,7 +62,9 @@ __host__ __device__ inline uint32_t wf_ctr(uint32_t ring_slot, uint32_t bounce, 
 // 8-15 % of the shade stage's stall samples).  The item space is therefore dealt out in chunks of WF_WORK_CHUNK
 // consecutive items to WF_WORK_SHARDS counters, one cache line each (chunk q belongs to shard q % SHARDS); a shade block
 // claims from shard (block % SHARDS).  Inside a shard the local index l counts that shard's items in increasing g.
+#ifndef WF_WORK_SHARDS
 #define WF_WORK_SHARDS 16
+#endif
 #define WF_WORK_CHUNK_LOG2 8
 // number of items g < n that belong to shard c
 __host__ __device__ inline unsigned long long wf_shard_count(unsigned long long n, uint32_t c) {
