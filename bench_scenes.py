@@ -3,7 +3,7 @@ meshes (the named .obj files are not in the reference mount: /root/reference/.MI
 Shared by bench.py, tools/ and the full-size GPU tests."""
 import math
 from webgpu_path_tracer_b200 import Scene, Camera, meshgen
-from tests import scenes
+from webgpu_path_tracer_b200 import standins as scenes
 
 _cache = {}
 

@@ -222,21 +222,3 @@ def test_bytes_only_present_equals_the_pinned_pow_for_every_float(default_scene)
     o.write_uniforms(5, 0, cam.viewMatrix)
     img = np.asarray(o.present()).reshape(-1, 4)
     assert np.array_equal(only[:, :3], np.rint(img[:, :3] * np.float32(255.0)).astype(np.uint8))
-
-
-@pytest.mark.parametrize("cfg", ["C2", "C3", "C4", "C5"])
-def test_full_size_primary_hits_and_radiance_fast_equals_exact(cfg):
-    """BASELINE.json's bar at the benchmark's own size: closest-hit primitive ids of every primary ray of the
-    full-size frame (1920x1080; C5: 3840x2160, 4 stratified samples, two meshes) bit-exact, and the radiance of the frame too (the fast path -- device-built
-    hierarchy, wide traversal, wavefront scheduling -- against the exact-mode kernel that walks the
-    reference's tree in the reference's order, itself pinned to the oracle at small sizes)."""
-    import bench_scenes
-    scene, cam, W, H, kw = bench_scenes.build(cfg)
-    e = setup(PathTracer(W, H, mode=MODE_EXACT, **kw), scene, cam, frame=3)
-    g = setup(PathTracer(W, H, mode=MODE_FAST, **kw), scene, cam, frame=3)
-    re_, te, ie, de = e.probe()
-    rg, tg, ig, dg = g.probe()
-    assert int((te != tg).sum()) == 0 and int((ie != ig).sum()) == 0
-    assert np.array_equal(bits(de), bits(dg))
-    assert np.array_equal(bits(re_), bits(rg))
-    assert (tg == 2).sum() > 10000          # the mesh is really in view

@@ -4,7 +4,6 @@ import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from webgpu_path_tracer_b200 import PathTracer, meshgen, MODE_EXACT, MODE_FAST
-from tests import scenes
 import bench_scenes
 
 cfg = sys.argv[1] if len(sys.argv) > 1 else "C2"

@@ -2,6 +2,7 @@
 // (K2), owns the wavefront pool, and drives the stage kernels (K3/K4) in batches without
 // stalling on the device: the only host<->device traffic per batch is one 4-byte "finished" flag
 // read back asynchronously, one batch behind.
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
@@ -20,7 +21,7 @@ struct FastState {
     // device-built hierarchy (K5, bvh_build.cu) that feeds K2 instead of binding 9
     BvhNode* own_bvh = nullptr; void* build_scratch = nullptr; uint32_t own_cap = 0;
     bool own_used = false;
-    WideBuildStats wstats = {0, 0, 0, 0};
+    WideBuildStats wstats = {0, 0, 0, 0, 127};
     // wavefront
     WfParams P;
     void* pool_mem = nullptr;
@@ -44,14 +45,19 @@ static const size_t PROF_QUADS = 2048;
 static void prof_fold(FastState* F) {
     if (!F->prof_used) return;
     cudaEventSynchronize(F->prof_ev[4 * (F->prof_used - 1) + 3]);
+    // developer aid: WGPT_PROF_DUMP=file appends one line per iteration (extend, shade, control + accumulate ms)
+    const char* dump_path = getenv("WGPT_PROF_DUMP");
+    FILE* dump = dump_path && *dump_path ? fopen(dump_path, "a") : nullptr;
     for (size_t i = 0; i < F->prof_used; i++) {
         float a = 0, b = 0, c2 = 0;
         cudaEventElapsedTime(&a, F->prof_ev[4 * i], F->prof_ev[4 * i + 1]);
         cudaEventElapsedTime(&b, F->prof_ev[4 * i + 1], F->prof_ev[4 * i + 2]);
         cudaEventElapsedTime(&c2, F->prof_ev[4 * i + 2], F->prof_ev[4 * i + 3]);
         F->prof_ms[0] += a; F->prof_ms[1] += b; F->prof_ms[2] += c2;
+        if (dump) fprintf(dump, "%.4f %.4f %.4f\n", a, b, c2);
         F->prof_launches[0] += 1; F->prof_launches[1] += 1; F->prof_launches[2] += 2;
     }
+    if (dump) { fprintf(dump, "\n"); fclose(dump); }
     F->prof_used = 0;
 }
 
@@ -75,7 +81,7 @@ static int ensure_wide(wgpt_ctx* c) {
     if (!c->wide_dirty) return WGPT_OK;
     const int n_bvh = (int)(c->dbytes[9] / 48), n_tri = (int)(c->dbytes[5] / 96);
     cudaError_t e;
-    if (n_bvh == 0) { F->wstats = {0, 0, 0, 0}; c->wide_dirty = false; return WGPT_OK; }
+    if (n_bvh == 0) { F->wstats = {0, 0, 0, 0, 127}; c->wide_dirty = false; return WGPT_OK; }
     const uint32_t cap = (uint32_t)std::max(16, n_bvh / 2 + 16);
     if (cap > F->wide_cap || (uint32_t)n_tri > F->wide_tri_cap) {
         if (F->wide_nodes) cudaFree(F->wide_nodes);
@@ -131,6 +137,10 @@ static int ensure_wide(wgpt_ctx* c) {
 static WideBvh wide_view(const wgpt_ctx* c, FastState* F) {
     WideBvh w; w.nodes = F->wide_nodes; w.tris = F->wide_tris; w.n_nodes = F->wstats.n_nodes; w.n_tris = F->wstats.n_tris;
     w.force_reference_walk = c->bvh_depth >= std::min(c->cfg.stack_size, 64) ? 1u : 0u;
+    // per-ray distance scale of the slab test (trace_wide.cuh): root cells of 2^-40 .. 2^40 world units are representable
+    const int er = (int)F->wstats.root_emax;
+    if (er < 127 - 40 || er > 127 + 40) w.force_reference_walk = 1u;
+    w.scale_k = (uint32_t)(395 - er);
     return w;
 }
 

@@ -54,7 +54,7 @@ __device__ __forceinline__ unsigned char quant8(float r, unsigned* slow) {
     return quant8_exact(r);
 }
 
-__global__ void __launch_bounds__(256) k_present(const float4* __restrict__ fb_in, float4* __restrict__ fb_clear,
+__global__ void __launch_bounds__(256) k_present(const float4* fb_in, float4* fb_clear,      // may alias (wgpt_present clears binding 3 in place): no __restrict__
                                                  float4* __restrict__ rgba_out, uchar4* __restrict__ rgba8_out,
                                                  uint32_t npix, float frameNum, int clear) {
     const bool frame_ok = frameNum > 8.67e-19f && frameNum < 1.15e18f;

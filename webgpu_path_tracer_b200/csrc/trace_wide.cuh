@@ -20,8 +20,9 @@ namespace wg {
 #endif
 
 struct WideRay {
-    float idx, idy, idz;      // 1/d with tiny components clamped (box tests only)
-    uint32_t octinv;          // bit 2/1/0 set when d.x/y/z >= 0
+    float idx, idy, idz;      // 1/d with tiny components clamped (box tests only); traversal rays: times the ray scale
+    uint32_t octinv;          // bit 2/1/0 set when the (clamped) d.x/y/z is positive: ALWAYS the sign of idx/idy/idz
+    float far_scale;          // traversal rays: 1.000002 * ray scale (closest distance -> scaled far cap)
 };
 
 __device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
@@ -34,7 +35,30 @@ __device__ __forceinline__ WideRay make_wide_ray(const Ray& r) {
     const float dz = fabsf(r.d.z) < eps ? copysignf(eps, r.d.z) : r.d.z;
     // box tests only (conservative, 2^-19 slack): the 1-ulp MUFU.RCP is enough, |d| is in [1e-12, ~1]
     w.idx = rcp_approx(dx); w.idy = rcp_approx(dy); w.idz = rcp_approx(dz);
-    w.octinv = (r.d.x >= 0.0f ? 4u : 0u) | (r.d.y >= 0.0f ? 2u : 0u) | (r.d.z >= 0.0f ? 1u : 0u);
+    // near / far planes are chosen from the sign BIT of the clamped component, i.e. of the reciprocal itself: a
+    // -0.0 component (shootRay's centre row, axis-aligned mirrors) clamps to -eps and must pair with the far planes
+    // (`d >= 0` is true for -0.0 and paired a negative reciprocal with the near planes: every child missed)
+    w.octinv = ((__float_as_uint(dx) >> 31) ? 0u : 4u) | ((__float_as_uint(dy) >> 31) ? 0u : 2u) | ((__float_as_uint(dz) >> 31) ? 0u : 1u);
+    w.far_scale = 1.000002f;
+    return w;
+}
+
+// The ray of a wide TRAVERSAL.  The slab test multiplies plane bytes by the cell size along the ray, cell_t =
+// 2^(e-127) / d, held as a binary16 operand of the mixed-precision FMA (wide_node_hits), so all ray distances of one
+// traversal are scaled by a per-ray power of two s (exact in f32; every comparison is between scaled values, so
+// nothing changes but the exponent range): s puts the largest cell any node can have along the axis of the
+// smallest |d| at 2^14..2^15, the top of binary16's range.  Cells only shrink below the root, so nothing overflows;
+// cells that fall below binary16's normal range lose precision, which the slab test's absolute slack covers.
+// scale_k = 395 - (largest plane exponent byte of the root node), from the host (WideBvh::scale_k).
+// `ok` = false: the scale does not fit f32 (caller-supplied rays with absurd directions): the reference walk decides.
+__device__ __forceinline__ WideRay make_wide_ray_scaled(const Ray& r, uint32_t scale_k, bool& ok) {
+    WideRay w = make_wide_ray(r);
+    const float m = fmaxf(fabsf(w.idx), fmaxf(fabsf(w.idy), fabsf(w.idz)));
+    const int se = (int)scale_k - (int)(__float_as_uint(m) >> 23);
+    ok = se >= 1 && se <= 254;
+    const float s = __uint_as_float((uint32_t)(ok ? se : 127) << 23);
+    w.idx *= s; w.idy *= s; w.idz *= s;
+    w.far_scale = 1.000002f * s;
     return w;
 }
 
@@ -53,19 +77,38 @@ __device__ __forceinline__ void wide_lut_init(unsigned char* lut) {
     __syncthreads();
 }
 
-// Two quantised plane bytes -> two floats (byte * 2^-24) without the conversion unit: PRMT builds
-// the half2 whose lanes are the SUBNORMAL halves 0x00bb (= b * 2^-24 exactly) and the widening
-// HADD2.F32 runs on the FMA pipe (I2F.U8 costs 8 issue cycles per warp on sm_100a, measured; 48
-// of them per node visit made the conversion unit the bottleneck of the whole traversal).  The
-// 2^24 is folded into the per-node scale.
-__device__ __forceinline__ void cvt2(uint32_t w, uint32_t sel, float& f0, float& f1) {
-    const uint32_t p = __byte_perm(w, 0u, sel);
-    const __half2 h = *reinterpret_cast<const __half2*>(&p);
-    f0 = __low2float(h); f1 = __high2float(h);
+// Plane bytes meet the ray in ONE instruction per plane: PRMT turns two bytes b of a plane word into the two
+// binary16 values 0x64bb = 1024 + b (exact), and the mixed-precision FMA of sm_100a (PTX fma.rn.f32.f16, SASS
+// FHFMA, which reads either half of a register) computes  t = (1024 + b) * cell_h + c  in f32, where cell_h is the
+// cell size along the ray rounded to binary16 and c = origin_t - 1024 * cell_h (one more FHFMA per axis and node).
+// Before: PRMT -> subnormal half -> widening HADD2.F32 -> FFMA, i.e. 48 more FMA-pipe instructions per node visit
+// (I2F.U8 runs on the XU pipe at 8 issue cycles per warp on sm_100a: never an option).
+// Error budget, in cells of the node grid: |b (cell_h - cell)| <= 255 * 2^-12 = 0.06226 (binary16 rounding of the
+// cell) + 2^-24 (1279 cell + 2 t) (f32 rounding of c and of the result).  K2 quantises every child box outwards
+// by 1/16 cell beyond floor / ceil (wide_bvh.cu), which covers the cell part; the relative part is the 2^-19 slack
+// below.  A cell below 2^-14 (scaled) is a binary16 subnormal with absolute error 2^-25: 255 of them are covered by
+// WIDE_ABS_SLACK on each side of the interval (applied at the comparison).
+#define WIDE_ABS_SLACK 1.52587890625e-05f     /* 2^-16, in scaled ray distance */
+// halves are picked INSIDE the asm block (mov.b32 {lo, hi}, r): 16-bit "h" operands made nvcc pass them through
+// local memory (STL.S16 / LDL.S16 in the traversal loop); this way ptxas sees 32-bit registers and emits R.H0 / R.H1
+#define WGPT_FHFMA(NAME, A, B)                                                                                  \
+    __device__ __forceinline__ float NAME(uint32_t a, uint32_t b, float c) {                                      \
+        float d;                                                                                                  \
+        asm("{\n\t.reg .b16 al, ah, bl, bh;\n\tmov.b32 {al, ah}, %1;\n\tmov.b32 {bl, bh}, %2;\n\t"                \
+            "fma.rn.f32.f16 %0, " A ", " B ", %3;\n\t}" : "=f"(d) : "r"(a), "r"(b), "f"(c));                      \
+        return d;                                                                                                 \
+    }
+WGPT_FHFMA(fhfma_ll, "al", "bl")      // a.lo * b.lo + c
+WGPT_FHFMA(fhfma_lh, "al", "bh")      // a.lo * b.hi + c
+WGPT_FHFMA(fhfma_hl, "ah", "bl")
+WGPT_FHFMA(fhfma_hh, "ah", "bh")
+__device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
+    const __half2 h = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t*>(&h);
 }
 
 // Intersects the 8 children of one wide node; returns the hit byte in SLOT order (bit s = the box
-// in slot s is hit over (0, closest]); empty slots never report.
+// in slot s is hit over (0, closest]); empty slots never report.  `wr` must come from make_wide_ray_scaled.
 __device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nodes, uint32_t ni, const Ray& ray,
                                                    const WideRay& wr, float closest, uint32_t& child_base,
                                                    uint32_t& tri_base, uint32_t& imask, uint32_t& lmask) {
@@ -75,19 +118,20 @@ __device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nod
     const uint4 n3 = __ldg(&nodes[5 * (size_t)ni + 3]);
     const uint4 n4 = __ldg(&nodes[5 * (size_t)ni + 4]);
     child_base = n1.x; tri_base = n1.y; imask = n0.w >> 24; lmask = n1.z & 0xffu;
-    // scale = 2^(e-127) * 2^24 (the subnormal-half conversion yields byte * 2^-24)
-    const float adjx = __uint_as_float(((n0.w & 0xffu) + 24u) << 23) * wr.idx;
-    const float adjy = __uint_as_float((((n0.w >> 8) & 0xffu) + 24u) << 23) * wr.idy;
-    const float adjz = __uint_as_float((((n0.w >> 16) & 0xffu) + 24u) << 23) * wr.idz;
-    const float ox = (__uint_as_float(n0.x) - ray.o.x) * wr.idx;
-    const float oy = (__uint_as_float(n0.y) - ray.o.y) * wr.idy;
-    const float oz = (__uint_as_float(n0.z) - ray.o.z) * wr.idz;
+    // cell size along the (scaled) ray, per axis, as binary16: x in the low half of cxy, y in the high half
+    const uint32_t cxy = pack_h2(__uint_as_float((n0.w & 0xffu) << 23) * wr.idx, __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * wr.idy);
+    const uint32_t cz = pack_h2(__uint_as_float(((n0.w >> 16) & 0xffu) << 23) * wr.idz, 0.0f);
+    // c = origin_t - 1024 cell_h (the absolute slack is applied once per slot, at the comparison)
+    const uint32_t m1024 = 0xE400u;                                            // binary16 -1024
+    const float cx = fhfma_ll(m1024, cxy, (__uint_as_float(n0.x) - ray.o.x) * wr.idx);
+    const float cy = fhfma_lh(m1024, cxy, (__uint_as_float(n0.y) - ray.o.y) * wr.idy);
+    const float cz_ = fhfma_ll(m1024, cz, (__uint_as_float(n0.z) - ray.o.z) * wr.idz);
     // near / far plane words by direction sign; [0] = slots 0..3, [1] = slots 4..7
     const bool px = (wr.octinv & 4u) != 0, py = (wr.octinv & 2u) != 0, pz = (wr.octinv & 1u) != 0;
     const uint32_t nx[2] = {px ? n2.x : n3.z, px ? n2.y : n3.w}, fx[2] = {px ? n3.z : n2.x, px ? n3.w : n2.y};
     const uint32_t ny[2] = {py ? n2.z : n4.x, py ? n2.w : n4.y}, fy[2] = {py ? n4.x : n2.z, py ? n4.y : n2.w};
     const uint32_t nz[2] = {pz ? n3.x : n4.z, pz ? n3.y : n4.w}, fz[2] = {pz ? n4.z : n3.x, pz ? n4.w : n3.y};
-    const float far_cap = closest * 1.000002f;
+    const float far_cap = fmaf(closest, wr.far_scale, WIDE_ABS_SLACK);
     // Straight-line code for all 8 slots (no divergence inside a node).  The sign of
     // the three differences below is the MISS flag; a funnel shift collects the flags, slot 7 first, so
     // slot s ends up in bit s.
@@ -96,19 +140,22 @@ __device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nod
     for (int pr = 3; pr >= 0; pr--) {
         const int w = pr >> 1;
         const uint32_t sel = (pr & 1) ? 0x4342u : 0x4140u;
-        float tlx[2], thx[2], tly[2], thy[2], tlz[2], thz[2];
-        cvt2(nx[w], sel, tlx[0], tlx[1]); cvt2(fx[w], sel, thx[0], thx[1]);
-        cvt2(ny[w], sel, tly[0], tly[1]); cvt2(fy[w], sel, thy[0], thy[1]);
-        cvt2(nz[w], sel, tlz[0], tlz[1]); cvt2(fz[w], sel, thz[0], thz[1]);
+        // two slots per PRMT: low half = slot 2 pr, high half = slot 2 pr + 1, each 0x64bb = 1024 + byte
+        const uint32_t hnx = __byte_perm(nx[w], 0x64646464u, sel), hfx = __byte_perm(fx[w], 0x64646464u, sel);
+        const uint32_t hny = __byte_perm(ny[w], 0x64646464u, sel), hfy = __byte_perm(fy[w], 0x64646464u, sel);
+        const uint32_t hnz = __byte_perm(nz[w], 0x64646464u, sel), hfz = __byte_perm(fz[w], 0x64646464u, sel);
         #pragma unroll
         for (int k = 1; k >= 0; k--) {
-            // hit <=> tlo3 <= thi3 * (1 + 2^-19)  and  tlo3 <= far  and  thi3 >= 0  (the box is not behind the
-            // origin); each test is the sign of one FMA-pipe result, OR-ed in a single LOP3
-            const float tlo3 = fmaxf(fmaxf(fmaf(tlx[k], adjx, ox), fmaf(tly[k], adjy, oy)), fmaf(tlz[k], adjz, oz));
-            const float thi3 = fminf(fminf(fmaf(thx[k], adjx, ox), fmaf(thy[k], adjy, oy)), fmaf(thz[k], adjz, oz));
-            const float d1 = fmaf(thi3, 1.000002f, -tlo3);
+            // hit <=> tlo3 - slack <= (thi3 + slack) * (1 + 2^-19)  and  tlo3 - slack <= far  and  thi3 + slack >= 0 (the
+            // box is not behind the origin); each test is the sign of one FMA-pipe result, OR-ed in a single LOP3
+            const float tlo3 = k ? fmaxf(fmaxf(fhfma_hl(hnx, cxy, cx), fhfma_hh(hny, cxy, cy)), fhfma_hl(hnz, cz, cz_))
+                                 : fmaxf(fmaxf(fhfma_ll(hnx, cxy, cx), fhfma_lh(hny, cxy, cy)), fhfma_ll(hnz, cz, cz_));
+            const float thi3 = k ? fminf(fminf(fhfma_hl(hfx, cxy, cx), fhfma_hh(hfy, cxy, cy)), fhfma_hl(hfz, cz, cz_))
+                                 : fminf(fminf(fhfma_ll(hfx, cxy, cx), fhfma_lh(hfy, cxy, cy)), fhfma_ll(hfz, cz, cz_));
+            const float hi_s = fmaf(thi3, 1.000002f, 3.0f * WIDE_ABS_SLACK);     // 2 slacks for the interval ends, 1 so that a thi3 just below 0 cannot flip d1
+            const float d1 = hi_s - tlo3;
             const float d2 = far_cap - tlo3;
-            const uint32_t d = __float_as_uint(d1) | __float_as_uint(d2) | __float_as_uint(thi3);
+            const uint32_t d = __float_as_uint(d1) | __float_as_uint(d2) | __float_as_uint(hi_s);
             miss = __funnelshift_l(d, miss, 1);
         }
     }
@@ -123,7 +170,9 @@ __device__ __forceinline__ bool hit_bvh_wide(const DeviceScene& S, const WideBvh
     ambiguous = false;
     if (WB.n_nodes == 0) return false;
     if (WB.force_reference_walk) { ambiguous = true; return false; }
-    const WideRay wr = make_wide_ray(ray);
+    bool ray_ok;
+    const WideRay wr = make_wide_ray_scaled(ray, WB.scale_k, ray_ok);
+    if (!ray_ok) { ambiguous = true; return false; }
     const unsigned char* lut_r = lut + (wr.octinv << 8);
     bool hit_anything = false;
     uint2 stack[WIDE_STACK];

@@ -99,16 +99,19 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
     const uint32_t lane = threadIdx.x & 31u;
     Counts c = {0, 0, 0, 0, 0, 0, 0, 0};
 
+    // Per-lane state is kept to what the walk itself needs (the kernel sits at its register cap): the ray direction is
+    // only used to set up the object-space ray (re-read from the slot in the rare multi-mesh case), the slot's tag and
+    // its sphere/quad result stay in the slot and are re-read at write-back, and of the triangle hit only
+    // (index, u, v, material) are carried -- its distance IS `closest`.
     bool has = false, exhausted = (n == 0);
     uint32_t slot = 0;
-    Ray ray; ray.o = ray.d = V3s(0.0f);
-    WideRay wr; wr.idx = wr.idy = wr.idz = 0.0f; wr.octinv = 0;
+    v3 ro = V3s(0.0f);
+    WideRay wr; wr.idx = wr.idy = wr.idz = 0.0f; wr.octinv = 0; wr.far_scale = 1.0f;
     ObjRayCache oc; oc.reset();
-    HitLite h;
-    h.t = 0.0f; h.kind = HIT_NONE; h.index = -1; h.uu = h.vv = 0.0f; h.mat_id = -1;
+    int h_index = -1, h_mat = -1;
+    float h_uu = 0.0f, h_vv = 0.0f;
     float closest = WGPT_MAX_FLOAT;
-    bool hit_t = false, hit_a = false, ambiguous = false, tie = false;
-    uint32_t tag0 = 0;           // tag of the slot as shade left it (kind / material of the sphere-quad hit)
+    bool hit_t = false, ambiguous = false, tie = false;
     uint2 G = make_uint2(0u, 0u);
     uint32_t tm = 0, tri_base = 0, tri_lmask = 0;   // parked candidate triangles of the last node visited: hit leaf slots, first
                                                     // packed triangle, leaf-slot mask (triangle of slot b = tri_base + popc(lmask below b))
@@ -122,6 +125,7 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
     while (true) {
         // ---- lanes whose walk is over write their result back and free the lane ----
         if (has && tm == 0u && (pk & 0xffu) == 0u && !(G.y & 0xff000000u) && sp == 0) {
+            const uint32_t tag0 = __float_as_uint(P.pool.x[slot].x);      // the slot as shade left it (kind / material of the sphere-quad hit)
             if (ambiguous | tie) {
                 // equal-distance triangles or a stack overflow: the reference-order walk decides.  The slot
                 // still holds the ray and its sphere/quad result; it is only MARKED here and the shade stage
@@ -138,20 +142,23 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     }
                 }
             } else {
+                const bool hit_a = wf_tag_kind(tag0) != HIT_NONE;
                 const bool hit = hit_a | hit_t;
-                const int cls = hit ? (int)__ldg(&S.materials[h.mat_id].material_type) : WF_CLS_MISS;
-                uint32_t tag = (tag0 & ~0xf0u) | ((uint32_t)cls << 4);          // the sphere/quad hit (or the miss) stands
+                const int mat = hit_t ? h_mat : wf_tag_mat(tag0);
+                const int cls = hit ? (int)__ldg(&S.materials[mat].material_type) : WF_CLS_MISS;
                 if (hit_t) {
-                    tag = wf_tag(HIT_TRI, cls, h.mat_id);
-                    reinterpret_cast<float*>(&P.pool.e0[slot])[3] = h.t;
-                    P.pool.x[slot] = make_float4(__uint_as_float(tag), __int_as_float(h.index), h.uu, h.vv);
+                    reinterpret_cast<float*>(&P.pool.e0[slot])[3] = closest;
+                    P.pool.x[slot] = make_float4(__uint_as_float(wf_tag(HIT_TRI, cls, mat)), __int_as_float(h_index), h_uu, h_vv);
                 } else {
-                    reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = tag;
+                    reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = (tag0 & ~0xf0u) | ((uint32_t)cls << 4);   // the sphere/quad hit (or the miss) stands
                 }
                 if (P.prim_type) {
                     const float4 e1v = P.pool.e1[slot], s1v = P.pool.s1[slot];
                     if ((__float_as_uint(e1v.w) & WF_CTR_FIRST_QUERY_MASK) == 0u) {                // first query of the item: the primary ray
-                        if (!hit_t) h.index = __float_as_int(P.pool.x[slot].y);
+                        HitLite h;
+                        h.kind = hit_t ? (int)HIT_TRI : wf_tag_kind(tag0); h.mat_id = mat; h.uu = h_uu; h.vv = h_vv;
+                        h.index = hit_t ? h_index : __float_as_int(P.pool.x[slot].y);
+                        h.t = hit_t ? closest : P.pool.e0[slot].w;
                         write_probe(S, P, __float_as_uint(s1v.w), hit, h);
                     }
                 }
@@ -172,13 +179,11 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     if (idx < n) {
                         slot = P.q_extend[idx];
                         const float4 o4 = P.pool.e0[slot], d4 = P.pool.e1[slot];
-                        tag0 = __float_as_uint(P.pool.x[slot].x);
-                        ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
-                        // sphere/quad result carried in by shade; its index stays in the slot (x.y), which
-                        // this stage only overwrites when a triangle wins
-                        h.t = o4.w; h.uu = 0.0f; h.vv = 0.0f; h.kind = wf_tag_kind(tag0); h.index = -1; h.mat_id = wf_tag_mat(tag0);
-                        hit_a = h.kind != HIT_NONE;
-                        closest = hit_a ? o4.w : WGPT_MAX_FLOAT;
+                        const uint32_t tag0 = __float_as_uint(P.pool.x[slot].x);
+                        Ray ray; ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(d4.x, d4.y, d4.z);
+                        ro = ray.o;
+                        // sphere/quad result carried in by shade: only its distance matters here
+                        closest = wf_tag_kind(tag0) != HIT_NONE ? o4.w : WGPT_MAX_FLOAT;
                         oc.reset();
 #ifndef WF_NO_OBJRAY_AT_FETCH
                         // One mesh in the scene: its object-space ray (common.wgsl:193-197) is set up here, where at least
@@ -186,9 +191,10 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                         if (S.NUM_MESHES == 1) oc.fetch(S, 0, ray);
 #endif
                         hit_t = false; ambiguous = false; tie = false; sp = 0; tm = 0; pk = 0;
-                        wr = make_wide_ray(ray);
+                        bool ray_ok;
+                        wr = make_wide_ray_scaled(ray, WB.scale_k, ray_ok);
                         G = make_uint2(0u, 0x80000000u);
-                        if (WB.force_reference_walk) { ambiguous = true; G.y = 0u; }     // marked at once: the reference walk decides
+                        if (WB.force_reference_walk || !ray_ok) { ambiguous = true; G.y = 0u; }     // marked at once: the reference walk decides
                         has = true;
                     }
                 }
@@ -216,32 +222,46 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                     const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << sl) & 0xffu);
                     uint32_t child_base, imask, lmask;
                     if (COUNT) c.nodes++;
-                    const uint32_t hits = wide_node_hits(WB.nodes, G.x + rel, ray, wr, closest, child_base, tri_base, imask, lmask);
+                    Ray rr; rr.o = ro; rr.d = ro;                  // (wide_node_hits only reads the origin)
+                    const uint32_t hits = wide_node_hits(WB.nodes, G.x + rel, rr, wr, closest, child_base, tri_base, imask, lmask);
                     G = make_uint2(child_base, ((uint32_t)s_lut[(wr.octinv << 8) | (hits & imask)] << 24) | imask);
                     tm = hits & lmask; tri_lmask = lmask;
                     if (tm != 0u && (pk & 0xffu) == 0u) { pk = tm | (lmask << 8); ptri_base = tri_base; tm = 0u; }
+#ifdef WF_PREFETCH
+                    if (G.y & 0xff000000u) {        // the child this lane descends into next: start its fetch before the votes / triangle phase
+                        const uint32_t bit2 = 31u - (uint32_t)__clz((int)(G.y & 0xff000000u));
+                        const uint32_t sl2 = (bit2 - 24u) ^ wr.octinv;
+                        const uint4* nx = &WB.nodes[5 * (size_t)(G.x + __popc(G.y & ~(0xffffffffu << sl2) & 0xffu))];
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(nx));
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(nx + 4));
+                    }
+#endif
                 }
             }
             // ---- triangle phase: one parked triangle per lane, once enough lanes have one ----
             const uint32_t m_tri = __ballot_sync(0xffffffffu, has && (pk & 0xffu) != 0u);
             const uint32_t m_node = __ballot_sync(0xffffffffu, has && tm == 0u && ((G.y & 0xff000000u) || sp > 0));
             const int n_tri = __popc(m_tri), n_node = __popc(m_node);
-                        if (n_tri >= WF_TRI_BATCH || (n_tri > 0 && n_tri * WF_TRI_ADAPT >= n_node)) {
+            if (n_tri >= WF_TRI_BATCH || (n_tri > 0 && n_tri * WF_TRI_ADAPT >= n_node)) {
                 if (has && (pk & 0xffu) != 0u) {
                     const int b = __ffs((int)pk) - 1;
                     const float4* t = &WB.tris[3 * (size_t)(ptri_base + (uint32_t)__popc((pk >> 8) & ~(0xffffffffu << b)))];
                     pk &= pk - 1u;
                     if ((pk & 0xffu) == 0u) { pk = tm | (tri_lmask << 8); ptri_base = tri_base; tm = 0u; }     // next set (possibly empty)
                     const float4 A = __ldg(&t[0]), B = __ldg(&t[1]), C = __ldg(&t[2]);
-                    oc.fetch(S, __float_as_int(B.w), ray);
+                    if (__float_as_int(B.w) != oc.mesh) {           // another mesh than the cached one: its object-space ray
+                        const float4 d4 = P.pool.e1[slot];
+                        Ray ray; ray.o = ro; ray.d = V3(d4.x, d4.y, d4.z);
+                        oc.fetch(S, __float_as_int(B.w), ray);
+                    }
                     float dst, uu, vv;
                     if (COUNT) c.tris++;
                     if (tri_test(V3(A.x, A.y, A.z), V3(B.x, B.y, B.z), V3(C.x, C.y, C.z), oc.oray, WGPT_RAY_TMIN, closest, dst, uu, vv)) {
                         tie = hit_t && dst == closest;                      // equal-distance triangles: visit order decides (resolved
-                                                                            // by k_wf_fallback); a strictly closer hit clears it
+                                                                            // by the shade stage); a strictly closer hit clears it
                         hit_t = true; closest = dst;
-                        h.t = dst; h.kind = HIT_TRI; h.index = __float_as_int(A.w); h.uu = uu; h.vv = vv;
-                        h.mat_id = oc.m.material_id;
+                        h_index = __float_as_int(A.w); h_uu = uu; h_vv = vv;
+                        h_mat = oc.m.material_id;
                     }
                 }
             }

@@ -17,7 +17,7 @@ struct BuildCtx {
     const Triangle* tris; int n_tris;
     uint4* out_nodes; float4* out_tris;
     uint32_t max_nodes;
-    uint32_t* counters;      // [0] nodes, [1] tris, [2],[3] queue counts, [4] levels, [5] overflow
+    uint32_t* counters;      // [0] nodes, [1] tris, [2],[3] queue counts, [4] levels, [5] overflow, [6] largest plane exponent byte of the root
     uint2* queue[2];
     // collapse plan (k_plan_*): which binary nodes become the children of a wide node
     int use_plan;
@@ -43,7 +43,7 @@ __device__ __forceinline__ float half_area(const BvhNode& n) {
 
 __global__ void k_wide_init(BuildCtx B) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
-        B.counters[0] = 1; B.counters[1] = 0; B.counters[2] = 1; B.counters[3] = 0; B.counters[4] = 0; B.counters[5] = 0;
+        B.counters[0] = 1; B.counters[1] = 0; B.counters[2] = 1; B.counters[3] = 0; B.counters[4] = 0; B.counters[5] = 0; B.counters[6] = 127;
         B.queue[0][0] = make_uint2(0u, 0u);      // (binary root, wide node 0)
     }
 }
@@ -194,18 +194,26 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
         for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
         for (int k = 0; k < n; k++) child_in_slot[slot_of[k]] = ch[k];
 
-        // ---- 3. quantisation frame: per-axis power-of-two scale with 255 steps covering the extent ----
-        uint32_t ebits[3]; float scale[3];
+        // ---- 3. quantisation frame: per-axis power-of-two cell with 255 cells covering the extent ----
+        // The frame starts 1/8 cell below the node box and every child plane is pushed 1/16 cell outwards before
+        // floor / ceil: that margin is the error budget of the traversal's binary16 cell size (trace_wide.cuh).
+        uint32_t ebits[3]; float scale[3]; float org[3];
         for (int a = 0; a < 3; a++) {
             const double ext = (double)hi[a] - (double)lo[a];
             int e = -126;
             if (ext > 0.0) { int k; frexp(ext, &k); e = k - 8; }       // ext in [2^(k-1), 2^k)
             if (e < -126) e = -126;
-            while (e < 127 && ldexp(255.0, e) < ext) e++;
-            if (e > 100) B.counters[5] = 1;                 // the traversal folds 2^24 into the scale (trace_wide.cuh cvt2)
+            for (;;) {
+                const double sc = ldexp(1.0, e);
+                org[a] = __double2float_rd((double)lo[a] - 0.125 * sc);
+                if (e >= 127 || ((double)hi[a] - (double)org[a]) / sc + 0.0625 <= 255.0) break;
+                e++;
+            }
+            if (e > 100) B.counters[5] = 1;                 // far outside any scene scale the ray scaling can hold
             ebits[a] = (uint32_t)(e + 127);
             scale[a] = __uint_as_float(ebits[a] << 23);
         }
+        if (wide_idx == 0u) B.counters[6] = max(ebits[0], max(ebits[1], ebits[2]));
 
         // ---- 4. count inner / leaf children, allocate, emit ----
         uint32_t imask = 0, n_inner = 0, n_leaf_tris = 0;
@@ -233,8 +241,8 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
             if (c < 0) continue;
             const BvhNode& cb = B.bvh[c];
             for (int a = 0; a < 3; a++) {
-                double l = floor(((double)cb.mn[a] - (double)lo[a]) / (double)scale[a]);
-                double h = ceil(((double)cb.mx[a] - (double)lo[a]) / (double)scale[a]);
+                double l = floor(((double)cb.mn[a] - (double)org[a]) / (double)scale[a] - 0.0625);
+                double h = ceil(((double)cb.mx[a] - (double)org[a]) / (double)scale[a] + 0.0625);
                 l = l < 0.0 ? 0.0 : (l > 255.0 ? 255.0 : l);
                 h = h < 0.0 ? 0.0 : (h > 255.0 ? 255.0 : h);
                 qlo[a][s] = (unsigned char)l; qhi[a][s] = (unsigned char)h;
@@ -257,7 +265,7 @@ __global__ void __launch_bounds__(128) k_wide_level(BuildCtx B, int parity) {
 
         auto pack4 = [](const unsigned char* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24); };
         uint4* o = &B.out_nodes[5 * (size_t)wide_idx];
-        o[0] = make_uint4(__float_as_uint(lo[0]), __float_as_uint(lo[1]), __float_as_uint(lo[2]),
+        o[0] = make_uint4(__float_as_uint(org[0]), __float_as_uint(org[1]), __float_as_uint(org[2]),
                           ebits[0] | (ebits[1] << 8) | (ebits[2] << 16) | (imask << 24));
         o[1] = make_uint4(child_base, tri_base, lmask, 0u);
         o[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
@@ -309,7 +317,7 @@ WideBuildStats wide_build_stats(const uint32_t* d_scratch, cudaStream_t stream) 
     uint32_t h[8] = {0};
     cudaMemcpyAsync(h, d_scratch, sizeof(h), cudaMemcpyDeviceToHost, stream);
     cudaStreamSynchronize(stream);
-    WideBuildStats s; s.n_nodes = h[0]; s.n_tris = h[1]; s.n_levels = h[4]; s.overflow = h[5];
+    WideBuildStats s; s.n_nodes = h[0]; s.n_tris = h[1]; s.n_levels = h[4]; s.overflow = h[5]; s.root_emax = h[6];
     return s;
 }
 
