@@ -187,6 +187,10 @@ int wgpt_write_buffer(wgpt_ctx* c, int binding, const void* data, size_t bytes) 
         return WGPT_OK;
     }
     cudaError_t e;
+    {   // frames already dispatched were dispatched with the OLD contents: finish them, and start a new wavefront afterwards
+        const int rc = fast_close(c);
+        if (rc) return rc;
+    }
     if (binding == 3) {
         if (bytes != c->dbytes[3]) return set_err(c, WGPT_E_INVALID, "framebuffer must be width*height*16 bytes");
         if ((e = cudaMemcpyAsync(c->dbuf[3], data, bytes, cudaMemcpyHostToDevice, c->stream)) != cudaSuccess) return cuda_err(c, e, "write framebuffer");

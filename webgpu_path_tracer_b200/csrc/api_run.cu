@@ -41,6 +41,8 @@ int wgpt_read_buffer(wgpt_ctx* c, int binding, void* out, size_t bytes) {
     }
     if (binding < 1 || binding > 9 || binding == 4) return set_err(c, WGPT_E_INVALID, "unknown binding");
     if (bytes != c->dbytes[binding]) return set_err(c, WGPT_E_INVALID, "size does not match the bound buffer");
+    int rc = fast_flush(c);                        // frames dispatched so far are in binding 3 before it is read
+    if (rc) return rc;
     cudaError_t e = cudaMemcpyAsync(out, c->dbuf[binding], bytes, cudaMemcpyDeviceToHost, c->stream);
     if (e != cudaSuccess) return cuda_err(c, e, "read_buffer");
     return cuda_err(c, cudaStreamSynchronize(c->stream), "read_buffer");
@@ -62,8 +64,11 @@ int wgpt_dispatch(wgpt_ctx* c, uint32_t workgroups) {
     cudaEventRecord(c->ev0, c->stream);
     c->last_launches = 0;
     if (c->cfg.mode == WGPT_MODE_FAST && c->cfg.max_bounces >= 1 && limit >= (uint32_t)c->cfg.width * c->cfg.height) {
-        rc = fast_render(c, (int)c->uniforms.frameNum, 1, c->uniforms.resetBuffer != 0.0f);
+        // the frame joins the living wavefront and the call returns (strata belong to wgpt_render: a dispatch is
+        // one whole frame in both modes)
+        rc = fast_dispatch(c, (int)c->uniforms.frameNum, c->uniforms.resetBuffer != 0.0f);
     } else {
+        if ((rc = fast_close(c)) != WGPT_OK) return rc;
         // (a partial dispatch -- fewer workgroups than pixels -- always takes the one-thread-per-pixel path)
         const DeviceScene S = make_device_scene(c, limit);
         launch_exact_frame(S, (float4*)c->dbuf[3], nullptr, nullptr, nullptr, nullptr, c->stream);
@@ -84,7 +89,7 @@ int wgpt_render(wgpt_ctx* c, int first_frame, int n_frames) {
     cudaEventRecord(c->ev0, c->stream);
     c->last_launches = 0;
     if (c->cfg.mode == WGPT_MODE_FAST && c->cfg.max_bounces >= 1) rc = fast_render(c, first_frame, n_frames, 0);
-    else rc = exact_render(c, first_frame, n_frames, 0xffffffffu);
+    else { rc = fast_close(c); if (!rc) rc = exact_render(c, first_frame, n_frames, 0xffffffffu); }
     if (n_frames > 0) c->uniforms.frameNum = (float)(first_frame + n_frames - 1);
     cudaEventRecord(c->ev1, c->stream);
     c->timing_valid = true;
@@ -95,6 +100,10 @@ int wgpt_present(wgpt_ctx* c, float* rgba_out, uint8_t* rgba8_out) {
     if (!c) return WGPT_E_INVALID;
     if (!c->have_uniforms) return set_err(c, WGPT_E_STATE, "uniforms (binding 0) not written");
     cudaSetDevice(c->cfg.device);
+    {   // `fs` runs after the compute passes submitted before it (webgpu-utils.js:133,147: one in-order queue)
+        const int rc = fast_flush(c);
+        if (rc) return rc;
+    }
     const uint32_t npix = (uint32_t)c->cfg.width * c->cfg.height;
     HostScratch d_rgba, d_rgba8;
     cudaError_t e;
@@ -112,6 +121,7 @@ int wgpt_probe(wgpt_ctx* c, float* radiance_out, int32_t* prim_type, int32_t* pr
     int rc = ready(c);
     if (rc) return rc;
     cudaSetDevice(c->cfg.device);
+    if ((rc = fast_close(c)) != WGPT_OK) return rc;
     const size_t npix = (size_t)c->cfg.width * c->cfg.height;
     cudaMemsetAsync(c->d_radiance, 0, npix * 12, c->stream);
     cudaMemsetAsync(c->d_ptype, 0xff, npix * 4, c->stream);
@@ -128,6 +138,7 @@ int wgpt_probe(wgpt_ctx* c, float* radiance_out, int32_t* prim_type, int32_t* pr
         c->dbuf[3] = d_fb.p;
         rc = fast_render_probe(c, (int)c->uniforms.frameNum, 1, 1, c->d_ptype, c->d_pindex, c->d_pt);
         c->dbuf[3] = real_fb;
+        fast_close(c);                             // the scratch buffer goes away: nothing may append to this session
         if (rc) return rc;
         launch_fb_to_rgb((const float4*)d_fb.p, c->d_radiance, (uint32_t)npix, c->stream);
         if (radiance_out) cudaMemcpyAsync(radiance_out, c->d_radiance, npix * 12, cudaMemcpyDeviceToHost, c->stream);
@@ -183,6 +194,10 @@ int wgpt_set_counters(wgpt_ctx* c, int enabled) {
 int wgpt_counters(wgpt_ctx* c, wgpt_counter_block* out, int reset) {
     if (!c || !out) return WGPT_E_INVALID;
     cudaSetDevice(c->cfg.device);
+    {
+        const int rc = fast_flush(c);
+        if (rc) return rc;
+    }
     unsigned long long h[8];
     cudaError_t e = cudaMemcpyAsync(h, c->d_counters, 64, cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess && reset) e = cudaMemsetAsync(c->d_counters, 0, 64, c->stream);
@@ -218,6 +233,8 @@ int wgpt_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]) {
 int wgpt_synchronize(wgpt_ctx* c) {
     if (!c) return WGPT_E_INVALID;
     cudaSetDevice(c->cfg.device);
+    const int rc = fast_flush(c);
+    if (rc) return rc;
     return cuda_err(c, cudaStreamSynchronize(c->stream), "synchronize");
 }
 

@@ -47,6 +47,9 @@ int validate_scene(wgpt_ctx* c);
 
 // fast.cu
 int fast_render(wgpt_ctx* c, int first_frame, int n_frames, int reset_first);
+int fast_dispatch(wgpt_ctx* c, int frame, int reset_first);      // non-blocking: the frame joins the open wavefront session
+int fast_flush(wgpt_ctx* c);                                      // run the open session until its frames are in binding 3
+int fast_close(wgpt_ctx* c);                                      // flush, and nothing may append to the session afterwards
 int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_first, int* d_ptype, int* d_pindex, float* d_pt);
 int fast_stats(wgpt_ctx* c, uint32_t out[8]);
 int fast_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]);

@@ -14,7 +14,19 @@
 
 namespace wg {
 
+// the open wavefront session (see fast_submit)
+struct Session {
+    bool open = false, pending = false, probe = false, counters_on = false;
+    int frame0 = 0, stride = 1, reset_first = 0;
+    uint32_t frames = 0;                   // frame ordinals submitted so far
+    Uniforms uniforms;                     // the view / screen size every frame of the session is rendered with
+    void* fb = nullptr;                    // the buffer the frames fold into (binding 3, or the probe's scratch)
+    WfParams P;
+};
+
 struct FastState {
+    Session sess;
+    unsigned extend_blocks[2] = {0, 0};    // persistent extend grid on this context's device, without / with counters
     // wide BVH
     uint4* wide_nodes = nullptr; float4* wide_tris = nullptr; uint32_t* wide_scratch = nullptr;
     uint32_t wide_cap = 0, wide_tri_cap = 0;
@@ -75,6 +87,8 @@ static int env_int(const char* name, int dflt) {
     return v && *v ? atoi(v) : dflt;
 }
 
+static bool transforms_consistent(const wgpt_ctx* c);
+
 static int ensure_wide(wgpt_ctx* c) {
     if (!c->fast) c->fast = new FastState();
     FastState* F = c->fast;
@@ -101,7 +115,7 @@ static int ensure_wide(wgpt_ctx* c) {
     // binding 5 (K5: better surface-area quality than the reference's median split); WGPT_BVH=reference
     // flattens binding 9 itself.  Binding 9 always remains the tree of exact mode and of the tie resolver.
     const char* which = getenv("WGPT_BVH");
-    bool own = !(which && which[0] == 'r') && n_tri > 0 && n_bvh == 2 * n_tri - 1 && c->dbytes[6] && c->dbytes[7];
+    bool own = !(which && which[0] == 'r') && n_tri > 0 && n_bvh == 2 * n_tri - 1 && c->dbytes[6] && c->dbytes[7] && transforms_consistent(c);
     for (int attempt = 0; attempt < 2; attempt++) {
         const BvhNode* src = (const BvhNode*)c->dbuf[9];
         if (own) {
@@ -140,13 +154,43 @@ static WideBvh wide_view(const wgpt_ctx* c, FastState* F) {
     // per-ray distance scale of the slab test (trace_wide.cuh): root cells of 2^-40 .. 2^40 world units are representable
     const int er = (int)F->wstats.root_emax;
     if (er < 127 - 40 || er > 127 + 40) w.force_reference_walk = 1u;
-    w.scale_k = (uint32_t)(395 - er);
+    w.scale_k = (uint32_t)(371 - er);
     return w;
+}
+
+// M * M^-1 == I to f32 accuracy for every transform of binding 7?  The reference's shaders never read modelMatrix
+// (common.wgsl:195 loads it, dead): hits are decided by invModelMatrix and the boxes of binding 9.  K5 takes its world
+// boxes from modelMatrix, so a caller whose modelMatrix is stale / identity / ill-conditioned must not get a device-built
+// tree: binding 9 is flattened instead.
+static bool transforms_consistent(const wgpt_ctx* c) {
+    const ModelTransform* t = (const ModelTransform*)c->hbuf[7].data();
+    const size_t n = c->hbuf[7].size() / sizeof(ModelTransform);
+    for (size_t i = 0; i < n; i++) {
+        const float* M = t[i].modelMatrix; const float* V = t[i].invModelMatrix;
+        for (int r = 0; r < 4; r++)
+            for (int col = 0; col < 4; col++) {
+                double acc = 0.0, mag = 0.0;
+                for (int k = 0; k < 4; k++) { const double p = (double)M[k * 4 + r] * (double)V[col * 4 + k]; acc += p; mag += p < 0 ? -p : p; }
+                const double err = acc - (r == col ? 1.0 : 0.0);
+                if (!((err < 0 ? -err : err) <= 4e-6 * (1.0 + mag))) return false;          // also false for NaN
+            }
+    }
+    return true;
+}
+
+static void free_pool(FastState* F) {
+    if (F->pool_mem) cudaFree(F->pool_mem);
+    if (F->h_flag) cudaFreeHost(F->h_flag);
+    if (F->flag_ev[0]) cudaEventDestroy(F->flag_ev[0]);
+    if (F->flag_ev[1]) cudaEventDestroy(F->flag_ev[1]);
+    F->pool_mem = nullptr; F->h_flag = nullptr; F->flag_ev[0] = F->flag_ev[1] = nullptr;
+    F->pool_ready = false;
 }
 
 static int ensure_pool(wgpt_ctx* c) {
     FastState* F = c->fast;
     if (F->pool_ready) return WGPT_OK;
+    free_pool(F);                                      // leftovers of a failed attempt
     const uint32_t npix = (uint32_t)c->cfg.width * c->cfg.height;
     uint32_t cap = (uint32_t)env_int("WGPT_POOL", 0);
     if (!cap) cap = std::min<uint64_t>(1u << 23, (uint64_t)c->shard_pixels * 4);
@@ -157,12 +201,19 @@ static int ensure_pool(wgpt_ctx* c) {
     uint32_t ring = (uint32_t)env_int("WGPT_RING", 0);
     if (!ring) ring = (uint32_t)std::min<uint64_t>(WF_MAX_RING, std::max<uint64_t>(64, (8ull << 30) / ((uint64_t)npix * 16)));
     ring = std::max(2u, std::min<uint32_t>(ring, WF_MAX_RING));
-    // one allocation, carved into 16-byte-aligned arrays
+    // one allocation, carved into 16-byte-aligned arrays; when the device cannot give that much (a smaller GPU, several
+    // contexts or ranks on one GPU) the staging ring is halved down to 2 frames before giving up
     const size_t per_slot = WF_BYTES_PER_SLOT;
-    const size_t bytes = (size_t)cap * per_slot + (size_t)ring * npix * 16 + (size_t)cap / WF_SHADE_THREADS / 8 + WF_FRONT_BLOCKS * 4 + WF_WORK_SHARDS * 128 + 56 * 256;
-    cudaError_t e;
-    if ((e = cudaMalloc(&F->pool_mem, bytes)) != cudaSuccess) return cuda_err(c, e, "wavefront pool alloc");
-    if ((e = cudaMemsetAsync(F->pool_mem, 0, bytes, c->stream)) != cudaSuccess) return cuda_err(c, e, "wavefront pool clear");
+    size_t bytes = 0;
+    cudaError_t e = cudaSuccess;
+    for (;; ring = std::max(2u, ring / 2)) {
+        bytes = (size_t)cap * per_slot + (size_t)ring * npix * 16 + (size_t)cap / WF_SHADE_THREADS / 8 + WF_FRONT_BLOCKS * 4 + WF_WORK_SHARDS * 128 + 56 * 256;
+        e = cudaMalloc(&F->pool_mem, bytes);
+        if (e != cudaErrorMemoryAllocation || ring == 2) break;
+        cudaGetLastError();
+    }
+    if (e != cudaSuccess) { F->pool_mem = nullptr; return cuda_err(c, e, "wavefront pool alloc"); }
+    if ((e = cudaMemsetAsync(F->pool_mem, 0, bytes, c->stream)) != cudaSuccess) { free_pool(F); return cuda_err(c, e, "wavefront pool clear"); }
     char* p = (char*)F->pool_mem;
     auto carve = [&](size_t n) { char* r = p; p += (n + 255) & ~(size_t)255; return r; };
     WfParams& P = F->P;
@@ -181,14 +232,15 @@ static int ensure_pool(wgpt_ctx* c) {
     P.ring = ring;
     P.items_per_frame = c->shard_pixels;
     P.inv_items_per_frame = 1.0 / (double)(c->shard_pixels ? c->shard_pixels : 1u);
-    if ((size_t)(p - (char*)F->pool_mem) > bytes) return set_err(c, WGPT_E_NOMEM, "pool carve overflow");
+    if ((size_t)(p - (char*)F->pool_mem) > bytes) { free_pool(F); return set_err(c, WGPT_E_NOMEM, "pool carve overflow"); }
     F->capacity = cap; F->ring = ring;
-    if ((e = cudaMallocHost((void**)&F->h_flag, 64)) != cudaSuccess) return cuda_err(c, e, "pinned flag");
+    if ((e = cudaMallocHost((void**)&F->h_flag, 64)) != cudaSuccess) { free_pool(F); return cuda_err(c, e, "pinned flag"); }
     memset(F->h_flag, 0, 64);
-    cudaEventCreateWithFlags(&F->flag_ev[0], cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&F->flag_ev[1], cudaEventDisableTiming);
-    if ((e = cudaMalloc((void**)&F->d_fallbacks, 4)) != cudaSuccess) return cuda_err(c, e, "fallback counter");
-    cudaMemsetAsync(F->d_fallbacks, 0, 4, c->stream);
+    if ((e = cudaEventCreateWithFlags(&F->flag_ev[0], cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&F->flag_ev[1], cudaEventDisableTiming)) != cudaSuccess) { free_pool(F); return cuda_err(c, e, "wavefront pool"); }
+    // the persistent extend grid of THIS context's device (a process may drive several devices)
+    F->extend_blocks[0] = wf_extend_grid(false);
+    F->extend_blocks[1] = wf_extend_grid(true);
     F->pool_ready = true;
     return WGPT_OK;
 }
@@ -203,36 +255,43 @@ static int check_materials(wgpt_ctx* c) {
     return WGPT_OK;
 }
 
-int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_first, int* d_ptype, int* d_pindex, float* d_pt) {
-    int rc = check_materials(c);
-    if (rc) return rc;
-    if (c->cfg.max_bounces > WF_MAX_BOUNCE_FIELD || c->cfg.num_samples > WF_MAX_SAMPLE_FIELD)
-        return set_err(c, WGPT_E_INVALID, "fast mode packs the bounce / sample counters: max_bounces <= 1023, num_samples <= 16383");
-    if ((rc = ensure_wide(c)) != WGPT_OK) return rc;
-    if ((rc = ensure_pool(c)) != WGPT_OK) return rc;
+// ---- the wavefront SESSION --------------------------------------------------------------------------------------
+// A session is one living wavefront: the frames submitted so far (frame0, frame0 + stride, ...), the uniforms they
+// are rendered with, the framebuffer they fold into.  wgpt_render opens one, pumps iterations until the device reports
+// that every frame has been folded, and leaves it open; wgpt_dispatch APPENDS its frame to the open session when it
+// continues it (next frame number, same view, resetBuffer = 0) and only enqueues a few iterations: the call returns
+// while the GPU works (webgpu-utils.js:125-134 submits and returns), later frames overlap the tails of earlier ones,
+// and whoever needs the pixels (present, read_buffer, counters, a buffer write, ...) flushes first.
+static bool same_view(const Uniforms& a, const Uniforms& b) {
+    return a.screenW == b.screenW && a.screenH == b.screenH && memcmp(a.viewMatrix, b.viewMatrix, sizeof(a.viewMatrix)) == 0;
+}
+
+int fast_pump(wgpt_ctx* c, int iterations) {
     FastState* F = c->fast;
-    // frames of this strata shard: f in [first, first+n) with f % world == rank
-    const int world = c->cfg.strata_world, rank = c->cfg.strata_rank;
-    int f0 = first_frame;
-    while (world > 1 && (f0 % world) != rank) f0++;
-    const int last = first_frame + n_frames;
-    const uint32_t my_frames = f0 < last ? (uint32_t)((last - 1 - f0) / world + 1) : 0u;
-    if (my_frames == 0) return WGPT_OK;
-    WfParams P = F->P;
-    P.frame0 = f0; P.frame_stride = world;
-    P.bvh_depth = c->bvh_depth;
-    P.prim_type = d_ptype; P.prim_index = d_pindex; P.prim_t = d_pt;
-    const DeviceScene S = make_device_scene(c, 0xffffffffu);
+    if (!F || !F->sess.open) return WGPT_OK;
+    Session& s = F->sess;
+    DeviceScene S = make_device_scene(c, 0xffffffffu);
+    S.uniforms = s.uniforms;                               // the view the session's frames were submitted with
+    S.counters = s.counters_on ? c->d_counters : nullptr;
     const WideBvh WB = wide_view(c, F);
-    wf_launch_init(P, my_frames, c->stream);
-    c->last_launches += 1;
+    for (int i = 0; i < iterations; i++)
+        wf_launch_iteration(S, WB, s.P, (float4*)s.fb, s.reset_first, F->extend_blocks[S.counters ? 1 : 0], c->stream,
+                            c->stage_profiling ? prof_next(F) : nullptr);
+    c->last_launches += (uint64_t)iterations * WF_LAUNCHES_PER_ITERATION;
+    return cuda_err(c, cudaGetLastError(), "wavefront iteration");
+}
+
+// runs the open session until every submitted frame is in the framebuffer (the device stays one batch ahead of the
+// host: the only traffic is one 4-byte "finished" flag per batch, read back asynchronously)
+int fast_flush(wgpt_ctx* c) {
+    FastState* F = c->fast;
+    if (!F || !F->sess.open || !F->sess.pending) return WGPT_OK;
     const int batch = std::max(1, env_int("WGPT_BATCH", 8));
     F->h_flag[0] = F->h_flag[1] = 0;
     for (int b = 0;; b++) {
-        for (int i = 0; i < batch; i++)
-            wf_launch_iteration(S, WB, P, (float4*)c->dbuf[3], reset_first, c->stream, c->stage_profiling ? prof_next(F) : nullptr);
-        c->last_launches += (uint64_t)batch * WF_LAUNCHES_PER_ITERATION;
-        cudaMemcpyAsync(&F->h_flag[b & 1], &P.ctl->finished, 4, cudaMemcpyDeviceToHost, c->stream);
+        int rc = fast_pump(c, batch);
+        if (rc) return rc;
+        cudaMemcpyAsync(&F->h_flag[b & 1], &F->sess.P.ctl->finished, 4, cudaMemcpyDeviceToHost, c->stream);
         cudaEventRecord(F->flag_ev[b & 1], c->stream);
         if (b >= 1) {                          // look at the previous batch's flag: the device stays one batch ahead
             cudaError_t e = cudaEventSynchronize(F->flag_ev[(b - 1) & 1]);
@@ -241,11 +300,76 @@ int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_firs
         }
         if (b > 4000000) return set_err(c, WGPT_E_STATE, "wavefront did not converge");
     }
-    return cuda_err(c, cudaGetLastError(), "fast_render");
+    F->sess.pending = false;
+    return cuda_err(c, cudaGetLastError(), "fast_flush");
+}
+
+// finishes and forgets the session (buffer writes, probes, mode changes): nothing may append to it afterwards
+int fast_close(wgpt_ctx* c) {
+    if (!c->fast) return WGPT_OK;
+    const int rc = fast_flush(c);
+    c->fast->sess.open = false; c->fast->sess.pending = false;
+    return rc;
+}
+
+// Adds frames first_frame .. first_frame + n_frames - 1 (those of this context's strata shard when `strata`) to the
+// wavefront: appended to the open session when they continue it, else a new session after the old one has drained.
+// Enqueues no iteration by itself.
+int fast_submit(wgpt_ctx* c, int first_frame, int n_frames, bool strata, int reset_first, int* d_ptype, int* d_pindex, float* d_pt) {
+    int rc = check_materials(c);
+    if (rc) return rc;
+    if (c->cfg.max_bounces > WF_MAX_BOUNCE_FIELD || c->cfg.num_samples > WF_MAX_SAMPLE_FIELD)
+        return set_err(c, WGPT_E_INVALID, "fast mode packs the bounce / sample counters: max_bounces <= 1023, num_samples <= 16383");
+    if ((rc = ensure_wide(c)) != WGPT_OK) return rc;
+    if ((rc = ensure_pool(c)) != WGPT_OK) return rc;
+    FastState* F = c->fast;
+    // frames of this strata shard: f in [first, first+n) with f % world == rank
+    const int world = strata ? c->cfg.strata_world : 1, rank = strata ? c->cfg.strata_rank : 0;
+    int f0 = first_frame;
+    while (world > 1 && (f0 % world) != rank) f0++;
+    const int last = first_frame + n_frames;
+    const uint32_t my_frames = f0 < last ? (uint32_t)((last - 1 - f0) / world + 1) : 0u;
+    if (my_frames == 0) return WGPT_OK;
+    Session& s = F->sess;
+    const bool probe = d_ptype || d_pindex || d_pt;
+    const bool append = s.open && !reset_first && !probe && !s.probe && s.stride == world &&
+                        (long long)f0 == (long long)s.frame0 + (long long)s.frames * world && same_view(s.uniforms, c->uniforms) &&
+                        s.fb == c->dbuf[3] && s.counters_on == c->counters_on && s.frames + my_frames < (1u << 30);
+    if (append) {
+        wf_launch_append(s.P, my_frames, c->stream);
+        s.frames += my_frames;
+    } else {
+        if ((rc = fast_close(c)) != WGPT_OK) return rc;
+        s.P = F->P;
+        s.P.frame0 = f0; s.P.frame_stride = world;
+        s.P.bvh_depth = c->bvh_depth;
+        s.P.prim_type = d_ptype; s.P.prim_index = d_pindex; s.P.prim_t = d_pt;
+        s.frame0 = f0; s.stride = world; s.frames = my_frames;
+        s.uniforms = c->uniforms; s.fb = c->dbuf[3]; s.reset_first = reset_first; s.probe = probe;
+        s.counters_on = c->counters_on;
+        wf_launch_init(s.P, my_frames, c->stream);
+        s.open = true;
+    }
+    c->last_launches += 1;
+    s.pending = true;
+    return cuda_err(c, cudaGetLastError(), "fast_submit");
+}
+
+int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_first, int* d_ptype, int* d_pindex, float* d_pt) {
+    int rc = fast_submit(c, first_frame, n_frames, true, reset_first, d_ptype, d_pindex, d_pt);
+    if (rc) return rc;
+    return fast_flush(c);
 }
 
 int fast_render(wgpt_ctx* c, int first_frame, int n_frames, int reset_first) {
     return fast_render_probe(c, first_frame, n_frames, reset_first, nullptr, nullptr, nullptr);
+}
+
+// wgpt_dispatch in fast mode: the frame joins the wavefront and the call returns after enqueueing a few iterations
+int fast_dispatch(wgpt_ctx* c, int frame, int reset_first) {
+    int rc = fast_submit(c, frame, 1, false, reset_first, nullptr, nullptr, nullptr);
+    if (rc) return rc;
+    return fast_pump(c, std::max(1, env_int("WGPT_DISPATCH_ITERS", 4)));
 }
 
 int fast_trace_rays(wgpt_ctx* c, int n, const float* d_rays, const uint32_t* d_seeds, int* d_type, int* d_index, float* d_t) {
@@ -269,6 +393,7 @@ int fast_stats(wgpt_ctx* c, uint32_t out[8]) {
     FastState* F = c->fast;
     if (!F) return WGPT_OK;
     out[0] = F->wstats.n_nodes; out[1] = F->wstats.n_tris; out[2] = F->wstats.n_levels; out[3] = F->capacity; out[4] = F->ring;
+    fast_flush(c);
     cudaStreamSynchronize(c->stream);
     if (F->pool_ready) {
         WfControl h;
@@ -304,10 +429,7 @@ void fast_destroy(wgpt_ctx* c) {
     if (F->wide_scratch) cudaFree(F->wide_scratch);
     if (F->own_bvh) cudaFree(F->own_bvh);
     if (F->build_scratch) cudaFree(F->build_scratch);
-    if (F->pool_mem) cudaFree(F->pool_mem);
-    if (F->h_flag) cudaFreeHost(F->h_flag);
-    if (F->flag_ev[0]) cudaEventDestroy(F->flag_ev[0]);
-    if (F->flag_ev[1]) cudaEventDestroy(F->flag_ev[1]);
+    free_pool(F);
     if (F->d_fallbacks) cudaFree(F->d_fallbacks);
     delete F;
     c->fast = nullptr;

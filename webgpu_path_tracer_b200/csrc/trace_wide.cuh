@@ -46,16 +46,22 @@ __device__ __forceinline__ WideRay make_wide_ray(const Ray& r) {
 // The ray of a wide TRAVERSAL.  The slab test multiplies plane bytes by the cell size along the ray, cell_t =
 // 2^(e-127) / d, held as a binary16 operand of the mixed-precision FMA (wide_node_hits), so all ray distances of one
 // traversal are scaled by a per-ray power of two s (exact in f32; every comparison is between scaled values, so
-// nothing changes but the exponent range): s puts the largest cell any node can have along the axis of the
-// smallest |d| at 2^14..2^15, the top of binary16's range.  Cells only shrink below the root, so nothing overflows;
-// cells that fall below binary16's normal range lose precision, which the slab test's absolute slack covers.
-// scale_k = 395 - (largest plane exponent byte of the root node), from the host (WideBvh::scale_k).
-// `ok` = false: the scale does not fit f32 (caller-supplied rays with absurd directions): the reference walk decides.
+// nothing changes but the exponent range): s puts 2^24 x (the largest cell any node can have along the axis of the
+// smallest |d|) at 2^14..2^15, the top of binary16's range (the 2^24 undoes the 2^-24 of the plane operand, a
+// binary16 subnormal).  Cells only shrink below the root, so nothing overflows; cells that fall below binary16's
+// normal range lose precision, which the slab test's absolute slack covers.
+// scale_k = 371 - (largest plane exponent byte of the root node), from the host (WideBvh::scale_k).
+// `ok` = false, the reference walk decides: the scale does not fit f32 (caller-supplied rays with absurd directions),
+// or one direction component is below 2^-20 of another -- the ray runs (almost) inside a plane of the grid, its
+// reciprocal there is 2^20 times the others, the common scale pushes every other axis into the absolute slack and the
+// walk would visit every node that plane cuts (measured: an exactly horizontal ray in the atrium's floor, 4,000 nodes,
+// 10 ms); about 6 rays in a million (cosine sampling returns an exact 0 component with probability 2^-25 per draw).
 __device__ __forceinline__ WideRay make_wide_ray_scaled(const Ray& r, uint32_t scale_k, bool& ok) {
     WideRay w = make_wide_ray(r);
-    const float m = fmaxf(fabsf(w.idx), fmaxf(fabsf(w.idy), fabsf(w.idz)));
+    const float ax = fabsf(w.idx), ay = fabsf(w.idy), az = fabsf(w.idz);
+    const float m = fmaxf(ax, fmaxf(ay, az)), mn = fminf(ax, fminf(ay, az));
     const int se = (int)scale_k - (int)(__float_as_uint(m) >> 23);
-    ok = se >= 1 && se <= 254;
+    ok = se >= 1 && se <= 254 && m <= mn * 1048576.0f;
     const float s = __uint_as_float((uint32_t)(ok ? se : 127) << 23);
     w.idx *= s; w.idy *= s; w.idz *= s;
     w.far_scale = 1.000002f * s;
@@ -78,19 +84,18 @@ __device__ __forceinline__ void wide_lut_init(unsigned char* lut) {
 }
 
 // Plane bytes meet the ray in ONE instruction per plane: PRMT turns two bytes b of a plane word into the two
-// binary16 values 0x64bb = 1024 + b (exact), and the mixed-precision FMA of sm_100a (PTX fma.rn.f32.f16, SASS
-// FHFMA, which reads either half of a register) computes  t = (1024 + b) * cell_h + c  in f32, where cell_h is the
-// cell size along the ray rounded to binary16 and c = origin_t - 1024 * cell_h (one more FHFMA per axis and node).
+// binary16 SUBNORMALS 0x00bb = b * 2^-24 (exact), and the mixed-precision FMA of sm_100a (PTX fma.rn.f32.f16, SASS
+// FHFMA, which reads either half of a register) computes  t = (b 2^-24) * cell_h + origin_t  in f32, where cell_h is
+// 2^24 x the cell size along the scaled ray, rounded to binary16.
 // Before: PRMT -> subnormal half -> widening HADD2.F32 -> FFMA, i.e. 48 more FMA-pipe instructions per node visit
 // (I2F.U8 runs on the XU pipe at 8 issue cycles per warp on sm_100a: never an option).
 // Error budget, in cells of the node grid: |b (cell_h - cell)| <= 255 * 2^-12 = 0.06226 (binary16 rounding of the
-// cell) + 2^-24 (1279 cell + 2 t) (f32 rounding of c and of the result).  K2 quantises every child box outwards
-// by 1/16 cell beyond floor / ceil (wide_bvh.cu), which covers the cell part; the relative part is the 2^-19 slack
-// below.  A cell below 2^-14 (scaled) is a binary16 subnormal with absolute error 2^-25: 255 of them are covered by
+// cell) + f32 rounding of origin_t and of the result.  K2 quantises every child box outwards by 1/16 cell beyond
+// floor / ceil (wide_bvh.cu), which covers the cell part; the relative part is the 2^-19 slack below.  A cell_h below
+// 2^-14 is a binary16 subnormal with absolute error 2^-25: times 255 * 2^-24 that is < 2^-41, covered by
 // WIDE_ABS_SLACK on each side of the interval (applied at the comparison).
-#define WIDE_ABS_SLACK 1.52587890625e-05f     /* 2^-16, in scaled ray distance */
-// halves are picked INSIDE the asm block (mov.b32 {lo, hi}, r): 16-bit "h" operands made nvcc pass them through
-// local memory (STL.S16 / LDL.S16 in the traversal loop); this way ptxas sees 32-bit registers and emits R.H0 / R.H1
+#define WIDE_ABS_SLACK 9.094947017729282e-13f     /* 2^-40, in scaled ray distance */
+// halves are picked INSIDE the asm block (mov.b32 {lo, hi}, r): ptxas sees 32-bit registers and emits R.H0 / R.H1
 #define WGPT_FHFMA(NAME, A, B)                                                                                  \
     __device__ __forceinline__ float NAME(uint32_t a, uint32_t b, float c) {                                      \
         float d;                                                                                                  \
@@ -107,25 +112,20 @@ __device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
     return *reinterpret_cast<const uint32_t*>(&h);
 }
 
-// Intersects the 8 children of one wide node; returns the hit byte in SLOT order (bit s = the box
-// in slot s is hit over (0, closest]); empty slots never report.  `wr` must come from make_wide_ray_scaled.
-__device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nodes, uint32_t ni, const Ray& ray,
-                                                   const WideRay& wr, float closest, uint32_t& child_base,
+// Intersects the 8 children of one wide node (its five 16-byte records n0..n4); returns the hit byte in SLOT order
+// (bit s = the box in slot s is hit over (0, closest]); empty slots never report.  `wr` must come from
+// make_wide_ray_scaled; only the origin of `ray` is read.
+__device__ __forceinline__ uint32_t wide_node_test(const uint4 n0, const uint4 n1, const uint4 n2, const uint4 n3, const uint4 n4,
+                                                   const Ray& ray, const WideRay& wr, float closest, uint32_t& child_base,
                                                    uint32_t& tri_base, uint32_t& imask, uint32_t& lmask) {
-    const uint4 n0 = __ldg(&nodes[5 * (size_t)ni]);
-    const uint4 n1 = __ldg(&nodes[5 * (size_t)ni + 1]);
-    const uint4 n2 = __ldg(&nodes[5 * (size_t)ni + 2]);
-    const uint4 n3 = __ldg(&nodes[5 * (size_t)ni + 3]);
-    const uint4 n4 = __ldg(&nodes[5 * (size_t)ni + 4]);
     child_base = n1.x; tri_base = n1.y; imask = n0.w >> 24; lmask = n1.z & 0xffu;
-    // cell size along the (scaled) ray, per axis, as binary16: x in the low half of cxy, y in the high half
-    const uint32_t cxy = pack_h2(__uint_as_float((n0.w & 0xffu) << 23) * wr.idx, __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * wr.idy);
-    const uint32_t cz = pack_h2(__uint_as_float(((n0.w >> 16) & 0xffu) << 23) * wr.idz, 0.0f);
-    // c = origin_t - 1024 cell_h (the absolute slack is applied once per slot, at the comparison)
-    const uint32_t m1024 = 0xE400u;                                            // binary16 -1024
-    const float cx = fhfma_ll(m1024, cxy, (__uint_as_float(n0.x) - ray.o.x) * wr.idx);
-    const float cy = fhfma_lh(m1024, cxy, (__uint_as_float(n0.y) - ray.o.y) * wr.idy);
-    const float cz_ = fhfma_ll(m1024, cz, (__uint_as_float(n0.z) - ray.o.z) * wr.idz);
+    // 2^24 x cell size along the (scaled) ray, per axis, as binary16: x in the low half of cxy, y in the high half
+    const uint32_t cxy = pack_h2(__uint_as_float(((n0.w & 0xffu) + 24u) << 23) * wr.idx, __uint_as_float((((n0.w >> 8) & 0xffu) + 24u) << 23) * wr.idy);
+    const uint32_t cz = pack_h2(__uint_as_float((((n0.w >> 16) & 0xffu) + 24u) << 23) * wr.idz, 0.0f);
+    // distance of the grid origin along each axis
+    const float cx = (__uint_as_float(n0.x) - ray.o.x) * wr.idx;
+    const float cy = (__uint_as_float(n0.y) - ray.o.y) * wr.idy;
+    const float cz_ = (__uint_as_float(n0.z) - ray.o.z) * wr.idz;
     // near / far plane words by direction sign; [0] = slots 0..3, [1] = slots 4..7
     const bool px = (wr.octinv & 4u) != 0, py = (wr.octinv & 2u) != 0, pz = (wr.octinv & 1u) != 0;
     const uint32_t nx[2] = {px ? n2.x : n3.z, px ? n2.y : n3.w}, fx[2] = {px ? n3.z : n2.x, px ? n3.w : n2.y};
@@ -140,10 +140,10 @@ __device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nod
     for (int pr = 3; pr >= 0; pr--) {
         const int w = pr >> 1;
         const uint32_t sel = (pr & 1) ? 0x4342u : 0x4140u;
-        // two slots per PRMT: low half = slot 2 pr, high half = slot 2 pr + 1, each 0x64bb = 1024 + byte
-        const uint32_t hnx = __byte_perm(nx[w], 0x64646464u, sel), hfx = __byte_perm(fx[w], 0x64646464u, sel);
-        const uint32_t hny = __byte_perm(ny[w], 0x64646464u, sel), hfy = __byte_perm(fy[w], 0x64646464u, sel);
-        const uint32_t hnz = __byte_perm(nz[w], 0x64646464u, sel), hfz = __byte_perm(fz[w], 0x64646464u, sel);
+        // two slots per PRMT: low half = slot 2 pr, high half = slot 2 pr + 1, each 0x00bb = byte * 2^-24
+        const uint32_t hnx = __byte_perm(nx[w], 0u, sel), hfx = __byte_perm(fx[w], 0u, sel);
+        const uint32_t hny = __byte_perm(ny[w], 0u, sel), hfy = __byte_perm(fy[w], 0u, sel);
+        const uint32_t hnz = __byte_perm(nz[w], 0u, sel), hfz = __byte_perm(fz[w], 0u, sel);
         #pragma unroll
         for (int k = 1; k >= 0; k--) {
             // hit <=> tlo3 - slack <= (thi3 + slack) * (1 + 2^-19)  and  tlo3 - slack <= far  and  thi3 + slack >= 0 (the
@@ -160,6 +160,14 @@ __device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nod
         }
     }
     return ~miss & (imask | lmask);
+}
+
+__device__ __forceinline__ uint32_t wide_node_hits(const uint4* __restrict__ nodes, uint32_t ni, const Ray& ray,
+                                                   const WideRay& wr, float closest, uint32_t& child_base,
+                                                   uint32_t& tri_base, uint32_t& imask, uint32_t& lmask) {
+    const uint4* n = &nodes[5 * (size_t)ni];
+    return wide_node_test(__ldg(&n[0]), __ldg(&n[1]), __ldg(&n[2]), __ldg(&n[3]), __ldg(&n[4]), ray, wr, closest,
+                          child_base, tri_base, imask, lmask);
 }
 
 // Triangle part of hitScene over the wide BVH.  `closest`/`h` carry in the sphere/quad result.

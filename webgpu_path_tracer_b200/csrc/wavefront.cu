@@ -18,6 +18,7 @@
 //   accumulate  K4: frames whose every item finished are added to binding 3 in frame order.
 // The RNG stream of a (pixel, frame) item lives in its slot, so the draw order equals the
 // reference's whatever the schedule; all arithmetic is pinned.
+#include <stdio.h>
 #include "wavefront.cuh"
 #include "shade.cuh"
 #include "camera.cuh"
@@ -49,6 +50,26 @@ __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
         c->acc_k = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
         c->finished = n_frames == 0 ? 1u : 0u; c->fallbacks = 0; c->iterations = 0;
         c->drain = 0; c->sparse = 0; c->live_read = 0; c->n_live = 0; c->n_live_next = 0; c->n_tie_blocks = 0;
+    }
+}
+
+// More frames join a wavefront that is still alive (or has just run dry): wgpt_dispatch appends one frame per call
+// to the open session instead of filling and draining the pool for every frame.  Slots that found no work left
+// (DEAD) poll the work counters again; the window, the totals and the drain bookkeeping restart from the new total.
+__global__ void k_wf_append(WfParams P, uint32_t more_frames) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P.pool.capacity) {
+        uint32_t* tag = reinterpret_cast<uint32_t*>(&P.pool.x[i]);
+        if (wf_tag_cls(*tag) == WF_CLS_DEAD) *tag = wf_tag(HIT_NONE, WF_CLS_IDLE, -1);
+    }
+    if (i == 0) {
+        WfControl* c = P.ctl;
+        c->n_frames += more_frames;
+        c->total_work += (unsigned long long)more_frames * P.items_per_frame;
+        const unsigned long long lim = (unsigned long long)(c->acc_k + P.ring) * P.items_per_frame;
+        c->work_limit = lim < c->total_work ? lim : c->total_work;
+        for (uint32_t k = 0; k < WF_WORK_SHARDS; k++) c->shard_lim[k] = wf_shard_count(c->work_limit, k);
+        c->finished = 0; c->drain = 0; c->sparse = 0; c->n_live = 0; c->n_live_next = 0;
     }
 }
 
@@ -89,6 +110,9 @@ __device__ __forceinline__ bool root_box_hit(const DeviceScene& S, const Ray& ra
 #ifndef WF_EXTEND_MINB
 #define WF_EXTEND_MINB 7
 #endif
+#ifndef WF_SSTACK
+#define WF_SSTACK 12        // traversal-stack levels kept in shared memory (8 B x 128 threads each)
+#endif
 template <bool COUNT>
 __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S, WideBvh WB, WfParams P) {
     __shared__ unsigned char s_lut[WIDE_LUT_BYTES];
@@ -119,12 +143,28 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
     // on with its next node instead of idling until enough lanes have triangles for a triangle phase; it only
     // blocks when a later visit finds leaf hits while the parked set is still waiting.
     uint32_t pk = 0, ptri_base = 0;                 // parked: hit leaf slots (bits 0-7) | leaf-slot mask << 8; first packed triangle
-    uint2 stack[WIDE_STACK];
+    // Traversal stack: the first WF_SSTACK levels live in SHARED memory ([level][thread]: conflict-free), deeper ones in
+    // local memory.  With the whole stack in local memory the pop was the largest single source of long-scoreboard
+    // stalls of the kernel (24 % of them, ncu source view: 28 warps x 32 lanes x 192 B of stack per SM do not stay in
+    // L1 next to the node and triangle lines); a wide-node walk pushes at most one entry per level, so 12 levels
+    // cover practically every ray of an 8-wide tree.  (Measured and dropped: copying the NEXT node global -> shared
+    // with cp.async right after each visit, so its latency runs under the votes and the triangle phase: the extra
+    // divergent advance step cost 14 % more warp instructions and the smaller L1 10 points of hit rate, extend +24 %.)
+    __shared__ uint2 s_stack[WF_SSTACK][128];
+    uint2 stack[WIDE_STACK - WF_SSTACK];
     int sp = 0;
+    unsigned dbg_nodes = 0;
 
     while (true) {
         // ---- lanes whose walk is over write their result back and free the lane ----
         if (has && tm == 0u && (pk & 0xffu) == 0u && !(G.y & 0xff000000u) && sp == 0) {
+#ifdef WF_DEBUG_LONG_WALKS
+            if (COUNT && dbg_nodes > WF_DEBUG_LONG_WALKS) {
+                const float4 d4 = P.pool.e1[slot];
+                printf("long walk: %u nodes o=(%g %g %g) d=(%g %g %g) id=(%g %g %g) closest=%g hit_t=%d amb=%d\n", dbg_nodes, ro.x, ro.y, ro.z,
+                       d4.x, d4.y, d4.z, wr.idx, wr.idy, wr.idz, closest, (int)hit_t, (int)ambiguous);
+            }
+#endif
             const uint32_t tag0 = __float_as_uint(P.pool.x[slot].x);      // the slot as shade left it (kind / material of the sphere-quad hit)
             if (ambiguous | tie) {
                 // equal-distance triangles or a stack overflow: the reference-order walk decides.  The slot
@@ -190,7 +230,7 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                         // a third of the warp fetches together; done lazily at the first triangle test it ran ~4 lanes wide.
                         if (S.NUM_MESHES == 1) oc.fetch(S, 0, ray);
 #endif
-                        hit_t = false; ambiguous = false; tie = false; sp = 0; tm = 0; pk = 0;
+                        hit_t = false; ambiguous = false; tie = false; sp = 0; tm = 0; pk = 0; dbg_nodes = 0;
                         bool ray_ok;
                         wr = make_wide_ray_scaled(ray, WB.scale_k, ray_ok);
                         G = make_uint2(0u, 0x80000000u);
@@ -204,7 +244,10 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
         if (__ballot_sync(0xffffffffu, has) == 0) break;        // queue drained and every lane finished
 
         while (true) {
-            if (has && tm == 0u && !(G.y & 0xff000000u) && sp > 0) G = stack[--sp];
+            if (has && tm == 0u && !(G.y & 0xff000000u) && sp > 0) {
+                --sp;
+                G = sp < WF_SSTACK ? s_stack[sp][threadIdx.x] : stack[sp - WF_SSTACK];
+            }
             // ---- node phase: one wide-node visit for every lane with a node pending and no parked triangles ----
             const bool node_work = has && tm == 0u && (G.y & 0xff000000u);
             if (node_work) {
@@ -214,28 +257,19 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                 bool overflow = false;
                 if (G.y & 0xff000000u) {
                     if (sp >= WIDE_STACK) overflow = true;          // deeper than the wide stack: reference walk decides
-                    else stack[sp++] = G;
+                    else { if (sp < WF_SSTACK) s_stack[sp][threadIdx.x] = G; else stack[sp - WF_SSTACK] = G; sp++; }
                 }
                 if (overflow) { ambiguous = true; G.y = 0u; sp = 0; pk = 0u; }
                 else {
                     const uint32_t sl = (bit - 24u) ^ wr.octinv;
                     const uint32_t rel = __popc(hits_imask & ~(0xffffffffu << sl) & 0xffu);
                     uint32_t child_base, imask, lmask;
-                    if (COUNT) c.nodes++;
+                    if (COUNT) { c.nodes++; dbg_nodes++; }
                     Ray rr; rr.o = ro; rr.d = ro;                  // (wide_node_hits only reads the origin)
                     const uint32_t hits = wide_node_hits(WB.nodes, G.x + rel, rr, wr, closest, child_base, tri_base, imask, lmask);
                     G = make_uint2(child_base, ((uint32_t)s_lut[(wr.octinv << 8) | (hits & imask)] << 24) | imask);
                     tm = hits & lmask; tri_lmask = lmask;
                     if (tm != 0u && (pk & 0xffu) == 0u) { pk = tm | (lmask << 8); ptri_base = tri_base; tm = 0u; }
-#ifdef WF_PREFETCH
-                    if (G.y & 0xff000000u) {        // the child this lane descends into next: start its fetch before the votes / triangle phase
-                        const uint32_t bit2 = 31u - (uint32_t)__clz((int)(G.y & 0xff000000u));
-                        const uint32_t sl2 = (bit2 - 24u) ^ wr.octinv;
-                        const uint4* nx = &WB.nodes[5 * (size_t)(G.x + __popc(G.y & ~(0xffffffffu << sl2) & 0xffu))];
-                        asm volatile("prefetch.global.L1 [%0];" :: "l"(nx));
-                        asm volatile("prefetch.global.L1 [%0];" :: "l"(nx + 4));
-                    }
-#endif
                 }
             }
             // ---- triangle phase: one parked triangle per lane, once enough lanes have one ----
@@ -697,19 +731,22 @@ void wf_launch_init(const WfParams& P, uint32_t n_frames, cudaStream_t stream) {
     k_wf_init<<<(P.pool.capacity + 255) / 256, 256, 0, stream>>>(P, n_frames);
 }
 
+void wf_launch_append(const WfParams& P, uint32_t more_frames, cudaStream_t stream) {
+    k_wf_append<<<(P.pool.capacity + 255) / 256, 256, 0, stream>>>(P, more_frames);
+}
+
+// persistent grid of the extend stage: exactly as many CTAs as fit on the CURRENT device (SM count x resident CTAs per SM)
+unsigned wf_extend_grid(bool counters) {
+    int dev = 0, sms = 148, per_sm = 4;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (counters) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_extend<true>, 128, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_extend<false>, 128, 0);
+    return (unsigned)(sms * (per_sm > 0 ? per_sm : 1));
+}
+
 void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
-                         cudaStream_t stream, cudaEvent_t* ev) {
-    // persistent grid: exactly as many CTAs as fit on the device (SM count x resident CTAs per SM)
-    static unsigned extend_blocks_cached[2] = {0, 0};
-    unsigned& extend_blocks = extend_blocks_cached[S.counters ? 1 : 0];
-    if (!extend_blocks) {
-        int dev = 0, sms = 148, per_sm = 4;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (S.counters) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_extend<true>, 128, 0);
-        else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_extend<false>, 128, 0);
-        extend_blocks = (unsigned)(sms * (per_sm > 0 ? per_sm : 1));
-    }
+                         unsigned extend_blocks, cudaStream_t stream, cudaEvent_t* ev) {
     if (ev) cudaEventRecord(ev[0], stream);
     if (S.counters) k_wf_extend<true><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);

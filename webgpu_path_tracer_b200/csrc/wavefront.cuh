@@ -128,9 +128,11 @@ struct WfParams {
 
 // wavefront.cu
 void wf_launch_init(const WfParams& P, uint32_t n_frames, cudaStream_t stream);
+void wf_launch_append(const WfParams& P, uint32_t more_frames, cudaStream_t stream);
+unsigned wf_extend_grid(bool counters);      // CTAs of the persistent extend grid on the current device
 // ev: optional 4 events recorded before extend, after extend, after shade, after accumulate
 void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
-                         cudaStream_t stream, cudaEvent_t* ev = nullptr);
+                         unsigned extend_blocks, cudaStream_t stream, cudaEvent_t* ev = nullptr);
 #define WF_LAUNCHES_PER_ITERATION 4
 void launch_trace_rays_wide(const DeviceScene& S, const WideBvh& WB, int n, const float* rays, const uint32_t* seeds,
                             int* out_type, int* out_index, float* out_t, uint32_t* fallbacks, cudaStream_t stream);

@@ -36,7 +36,7 @@ struct WideBvh {
     // The reference's stack guard (hitRay.wgsl:100-104) can fire: binding 9 is at least STACK_SIZE deep, so what
     // the reference returns depends on its own visit order for ANY ray.  Every ray then takes the reference walk.
     uint32_t force_reference_walk;
-    // 395 - (largest plane exponent byte of the root node): the per-ray power-of-two distance scale of the
+    // 371 - (largest plane exponent byte of the root node): the per-ray power-of-two distance scale of the
     // mixed-precision slab test (trace_wide.cuh make_wide_ray_scaled)
     uint32_t scale_k;
 };
