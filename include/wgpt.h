@@ -93,12 +93,18 @@ const char* wgpt_last_error(const wgpt_ctx* ctx);     /* ctx may be NULL: last c
 int wgpt_write_buffer(wgpt_ctx* ctx, int binding, const void* data, size_t bytes);
 /* device -> host copy of a binding (the reference never reads back; needed headless). */
 int wgpt_read_buffer(wgpt_ctx* ctx, int binding, void* out, size_t bytes);
-/* raw device pointer + size of a binding, for NCCL reductions on binding 3 by the host layer. */
+/* raw device pointer + size of a binding (zero-copy views for the host layer; call wgpt_synchronize first: frames
+ * submitted with wgpt_dispatch may still be in flight). */
 int wgpt_device_ptr(wgpt_ctx* ctx, int binding, void** dptr, size_t* bytes);
 
 /* One `computePass(...)`: one frame with the uniforms currently in binding 0
  * (main.wgsl:1-28).  `workgroups` is what the caller would pass to dispatchWorkgroups
- * (renderer.js:187-188: W*H/64 + 1); invocations with index >= W*H are masked. */
+ * (renderer.js:187-188: W*H/64 + 1); invocations with index >= W*H are masked.
+ * Enqueues and returns, like webgpu-utils.js:125-134 (submit): in fast mode the frame JOINS the living wavefront
+ * (consecutive frame numbers with the same view and resetBuffer = 0 share one session; anything else -- another
+ * view, a gap, a reset, a buffer write -- first finishes the frames already submitted, which keep the uniforms they
+ * were dispatched with).  present / read_buffer / counters / synchronize wait for the submitted frames.  A dispatch
+ * is one whole frame whatever the strata shard (strata belong to wgpt_render). */
 int wgpt_dispatch(wgpt_ctx* ctx, uint32_t workgroups);
 /* Batched form of the renderAnimation loop (renderer.js:163-188) without camera motion:
  * frames first_frame .. first_frame+n_frames-1, uniforms.frameNum advanced internally,
@@ -125,6 +131,10 @@ int wgpt_set_counters(wgpt_ctx* ctx, int enabled);
  * context's stream): total milliseconds and number of kernel launches issued. ---- */
 int wgpt_last_timing(wgpt_ctx* ctx, float* ms, uint64_t* launches);
 int wgpt_synchronize(wgpt_ctx* ctx);
+/* stopwatch on the context's stream: wgpt_timer_mark(ctx, 0) ... wgpt_timer_mark(ctx, 1); wgpt_timer_elapsed waits for
+ * mark 1 and returns the device time between the marks (renders AND reduces enqueued in between). */
+int wgpt_timer_mark(wgpt_ctx* ctx, int which);
+int wgpt_timer_elapsed(wgpt_ctx* ctx, float* ms);
 
 /* fast-mode introspection: the derived wide BVH, the wavefront pool, and how many rays had to be
  * re-traced with the reference-order binary walk (equal-distance triangles / stack overflow). */
@@ -161,6 +171,34 @@ int wgpt_k4_timing(wgpt_ctx* ctx, int kernel, int reps, float* ms_per_launch, ui
  * every float whose bit pattern lies in [first_bits, first_bits + count) ON THE GPU and returns the
  * number of differing bytes (must be 0) and how many inputs took the pinned path. */
 int wgpt_present_quant_check(wgpt_ctx* ctx, uint32_t first_bits, uint32_t count, uint64_t* mismatches, uint64_t* exact_path);
+
+/* ---- multi-GPU (csrc/mgpu.cu).  The scene is replicated; wgpt_config's tile_* / strata_* fields say
+ * which pixels / frames a context renders; the partial accumulation buffers are combined by ONE ncclReduce(sum) of
+ * binding 3 that the library issues on the context's stream, behind the render kernels (no host synchronisation).
+ * Tile shards have disjoint support, so their sum equals the single-GPU buffer bit for bit; frame strata change the
+ * per-pixel summation order (f32 rounding).  NCCL is resolved with dlopen at the first of these calls.
+ *
+ * One process per GPU: rank 0 calls wgpt_nccl_unique_id, the caller ships the 128 bytes to every rank (MPI,
+ * torch.distributed, a file ...), every rank calls wgpt_comm_init on its context (collective), then
+ * wgpt_reduce_framebuffer(ctx, root) after its wgpt_render calls (collective; root = -1: every rank gets the sum).
+ * The call enqueues and returns; wgpt_synchronize / wgpt_read_buffer / wgpt_present wait for it. */
+int wgpt_nccl_unique_id(void* id128);
+int wgpt_comm_init(wgpt_ctx* ctx, const void* id128, int rank, int world);
+int wgpt_reduce_framebuffer(wgpt_ctx* ctx, int root);
+
+/* One process, N devices: a group owns one context per device (rank r: tile shard r % tile_groups of strata shard
+ * r / tile_groups; cfg->device / tile_* / strata_* are overwritten per rank; devices == NULL: 0 .. n-1) and one host
+ * thread per context for the calls that block.  wgpt_group_reduce leaves the sum in rank `root`'s binding 3 and
+ * returns when it is there; wgpt_group_ctx(g, root) is then an ordinary context to read / present. */
+typedef struct wgpt_group wgpt_group;
+int  wgpt_group_create(const wgpt_config* cfg, int n_devices, const int* devices, int tile_groups, wgpt_group** out);
+void wgpt_group_destroy(wgpt_group* g);
+const char* wgpt_group_last_error(const wgpt_group* g);
+int  wgpt_group_size(const wgpt_group* g);
+wgpt_ctx* wgpt_group_ctx(wgpt_group* g, int rank);
+int  wgpt_group_write_buffer(wgpt_group* g, int binding, const void* data, size_t bytes);
+int  wgpt_group_render(wgpt_group* g, int first_frame, int n_frames);
+int  wgpt_group_reduce(wgpt_group* g, int root);
 
 #ifdef __cplusplus
 }

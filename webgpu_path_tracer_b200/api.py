@@ -19,7 +19,10 @@ COUNTER_NAMES = ("rays", "node_visits", "tri_tests", "sphere_tests", "quad_tests
 EXPORTS = ("wgpt_default_config", "wgpt_create", "wgpt_destroy", "wgpt_last_error", "wgpt_write_buffer",
            "wgpt_read_buffer", "wgpt_device_ptr", "wgpt_dispatch", "wgpt_render", "wgpt_present", "wgpt_probe",
            "wgpt_trace_rays", "wgpt_counters", "wgpt_set_counters", "wgpt_last_timing", "wgpt_synchronize",
-           "wgpt_pinned_math", "wgpt_fast_statistics", "wgpt_set_stage_profiling", "wgpt_stage_timings", "wgpt_k4_timing", "wgpt_present_quant_check")
+           "wgpt_pinned_math", "wgpt_fast_statistics", "wgpt_set_stage_profiling", "wgpt_stage_timings", "wgpt_k4_timing", "wgpt_present_quant_check",
+           "wgpt_timer_mark", "wgpt_timer_elapsed", "wgpt_nccl_unique_id", "wgpt_comm_init", "wgpt_reduce_framebuffer", "wgpt_group_create", "wgpt_group_destroy",
+           "wgpt_group_last_error", "wgpt_group_size", "wgpt_group_ctx", "wgpt_group_write_buffer", "wgpt_group_render",
+           "wgpt_group_reduce")
 
 
 class WgptError(RuntimeError):
@@ -82,9 +85,34 @@ def load_library(path=None):
     L.wgpt_fast_statistics.argtypes = [vp, C.POINTER(FastStats)]
     L.wgpt_set_stage_profiling.argtypes = [vp, i32]
     L.wgpt_stage_timings.argtypes = [vp, C.POINTER(C.c_float * 4), C.POINTER(C.c_uint64 * 4)]
+    L.wgpt_timer_mark.argtypes = [vp, i32]
+    L.wgpt_timer_elapsed.argtypes = [vp, C.POINTER(C.c_float)]
+    L.wgpt_nccl_unique_id.argtypes = [vp]
+    L.wgpt_comm_init.argtypes = [vp, vp, i32, i32]
+    L.wgpt_reduce_framebuffer.argtypes = [vp, i32]
+    L.wgpt_group_create.argtypes = [C.POINTER(Config), i32, vp, i32, C.POINTER(vp)]
+    L.wgpt_group_destroy.argtypes = [vp]
+    L.wgpt_group_destroy.restype = None
+    L.wgpt_group_last_error.argtypes = [vp]
+    L.wgpt_group_last_error.restype = C.c_char_p
+    L.wgpt_group_size.argtypes = [vp]
+    L.wgpt_group_ctx.argtypes = [vp, i32]
+    L.wgpt_group_ctx.restype = vp
+    L.wgpt_group_write_buffer.argtypes = [vp, i32, vp, sz]
+    L.wgpt_group_render.argtypes = [vp, i32, i32]
+    L.wgpt_group_reduce.argtypes = [vp, i32]
     if path is None:
         _lib = L
     return L
+
+
+def nccl_unique_id():
+    """128 opaque bytes for wgpt_comm_init: generated on ONE rank, shipped to the others by the caller."""
+    buf = (C.c_ubyte * 128)()
+    rc = load_library().wgpt_nccl_unique_id(buf)
+    if rc:
+        raise WgptError("wgpt_nccl_unique_id -> %d: %s" % (rc, load_library().wgpt_last_error(None).decode()))
+    return bytes(buf)
 
 
 def _p(a):
@@ -128,6 +156,15 @@ class PathTracer:
             self.close()
         except Exception:
             pass
+
+    # ---- multi-GPU, one process per GPU (include/wgpt.h, csrc/mgpu.cu) ----
+    def comm_init(self, unique_id, rank, world):
+        buf = (C.c_ubyte * 128).from_buffer_copy(bytes(unique_id))
+        self._ck(self.L.wgpt_comm_init(self.h, buf, int(rank), int(world)), "wgpt_comm_init")
+
+    def reduce_framebuffer(self, root=0):
+        """ncclReduce(sum) of binding 3 onto `root` (-1: all ranks), enqueued behind the renders on the context's stream."""
+        self._ck(self.L.wgpt_reduce_framebuffer(self.h, int(root)), "wgpt_reduce_framebuffer")
 
     # ---- buffers ----
     def write_buffer(self, binding, array):
@@ -174,6 +211,14 @@ class PathTracer:
 
     def synchronize(self):
         self._ck(self.L.wgpt_synchronize(self.h), "wgpt_synchronize")
+
+    def timer_mark(self, which):
+        self._ck(self.L.wgpt_timer_mark(self.h, int(which)), "wgpt_timer_mark")
+
+    def timer_elapsed(self):
+        ms = C.c_float()
+        self._ck(self.L.wgpt_timer_elapsed(self.h, C.byref(ms)), "wgpt_timer_elapsed")
+        return ms.value
 
     def last_timing(self):
         ms, n = C.c_float(), C.c_uint64()
@@ -238,3 +283,72 @@ class PathTracer:
         out = np.empty_like(x)
         self._ck(self.L.wgpt_pinned_math(self.h, names[fn], x.size, _p(x), _p(y), _p(out)), "wgpt_pinned_math")
         return out
+
+
+class _GroupMember(PathTracer):
+    """A context owned by a Group: same calls as PathTracer, destroyed with the group."""
+
+    def __init__(self, L, handle, W, H):          # no wgpt_create: the group made the context
+        self.L, self.h, self.W, self.H = L, C.c_void_p(handle), W, H
+
+    def close(self):
+        self.h = None
+
+
+class Group:
+    """wgpt_group: one process, N devices, tile x strata sharding, ncclReduce inside the library."""
+
+    def __init__(self, width, height, n_devices, tile_groups=1, devices=None, mode=MODE_FAST, num_samples=1, max_bounces=100,
+                 stratify=False, importance_sampling=False, stack_size=20, tile_rows=8):
+        self.L = load_library()
+        cfg = Config()
+        self.L.wgpt_default_config(C.byref(cfg))
+        cfg.width, cfg.height, cfg.mode = int(width), int(height), int(mode)
+        cfg.num_samples, cfg.max_bounces = int(num_samples), int(max_bounces)
+        cfg.stratify, cfg.importance_sampling, cfg.stack_size = int(stratify), int(importance_sampling), int(stack_size)
+        cfg.tile_rows = int(tile_rows)
+        self.W, self.H, self.n = int(width), int(height), int(n_devices)
+        devs = (C.c_int * self.n)(*devices) if devices is not None else None
+        self.h = C.c_void_p()
+        rc = self.L.wgpt_group_create(C.byref(cfg), self.n, devs, int(tile_groups), C.byref(self.h))
+        if rc:
+            self.h = None
+            raise WgptError("wgpt_group_create -> %d: %s" % (rc, self.L.wgpt_last_error(None).decode()))
+
+    def _ck(self, rc, what):
+        if rc:
+            raise WgptError("%s -> %d: %s" % (what, rc, self.L.wgpt_group_last_error(self.h).decode()))
+
+    def member(self, rank):
+        return _GroupMember(self.L, self.L.wgpt_group_ctx(self.h, int(rank)), self.W, self.H)
+
+    def write_buffer(self, binding, array):
+        a = np.ascontiguousarray(array)
+        self._ck(self.L.wgpt_group_write_buffer(self.h, binding, _p(a), a.nbytes), "wgpt_group_write_buffer(%d)" % binding)
+
+    def write_scene(self, buffers):
+        for b, a in buffers.items():
+            self.write_buffer(b, a)
+
+    def write_uniforms(self, frame_num, reset_buffer, view_matrix):
+        u = np.zeros(20, np.float32)
+        u[0], u[1], u[2], u[3] = self.W, self.H, frame_num, reset_buffer
+        u[4:20] = np.asarray(view_matrix, np.float32)
+        self.write_buffer(0, u)
+
+    def render(self, first_frame, n_frames):
+        self._ck(self.L.wgpt_group_render(self.h, int(first_frame), int(n_frames)), "wgpt_group_render")
+
+    def reduce(self, root=0):
+        self._ck(self.L.wgpt_group_reduce(self.h, int(root)), "wgpt_group_reduce")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.wgpt_group_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

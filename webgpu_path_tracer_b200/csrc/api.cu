@@ -160,6 +160,7 @@ void wgpt_destroy(wgpt_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    mgpu_destroy(c);
     fast_destroy(c);
     for (int i = 0; i < 10; i++) if (c->dbuf[i]) cudaFree(c->dbuf[i]);
     if (c->d_counters) cudaFree(c->d_counters);
@@ -169,6 +170,8 @@ void wgpt_destroy(wgpt_ctx* c) {
     if (c->d_pt) cudaFree(c->d_pt);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->tm_ev[0]) cudaEventDestroy(c->tm_ev[0]);
+    if (c->tm_ev[1]) cudaEventDestroy(c->tm_ev[1]);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }

@@ -251,6 +251,25 @@ int wgpt_last_timing(wgpt_ctx* c, float* ms, uint64_t* launches) {
     return WGPT_OK;
 }
 
+// Device-side stopwatch on the context's own stream (bench.py: a step is render + reduce, both enqueued there, and
+// torch.cuda.Event only sees torch's stream): mark(0) ... mark(1), then elapsed() waits for mark 1.
+int wgpt_timer_mark(wgpt_ctx* c, int which) {
+    if (!c || which < 0 || which > 1) return WGPT_E_INVALID;
+    cudaSetDevice(c->cfg.device);
+    cudaError_t e = cudaSuccess;
+    if (!c->tm_ev[0] && ((e = cudaEventCreate(&c->tm_ev[0])) != cudaSuccess || (e = cudaEventCreate(&c->tm_ev[1])) != cudaSuccess))
+        return cuda_err(c, e, "timer_mark");
+    return cuda_err(c, cudaEventRecord(c->tm_ev[which], c->stream), "timer_mark");
+}
+
+int wgpt_timer_elapsed(wgpt_ctx* c, float* ms) {
+    if (!c || !ms || !c->tm_ev[0]) return WGPT_E_INVALID;
+    cudaSetDevice(c->cfg.device);
+    cudaError_t e = cudaEventSynchronize(c->tm_ev[1]);
+    if (e == cudaSuccess) e = cudaEventElapsedTime(ms, c->tm_ev[0], c->tm_ev[1]);
+    return cuda_err(c, e, "timer_elapsed");
+}
+
 int wgpt_pinned_math(wgpt_ctx* c, int fn, int n, const float* x, const float* y, float* out) {
     if (!c || n < 0 || (n && (!x || !out)) || fn < 0 || fn > 7) return WGPT_E_INVALID;
     if (n == 0) return WGPT_OK;

@@ -22,6 +22,7 @@ struct wgpt_ctx {
     unsigned long long* d_counters = nullptr;
     bool counters_on = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t tm_ev[2] = {nullptr, nullptr};       // wgpt_timer_mark
     bool timing_valid = false;
     uint64_t last_launches = 0;
     uint32_t shard_pixels = 0;
@@ -34,6 +35,8 @@ struct wgpt_ctx {
     int tri_mesh_max = -1; bool tri_bad = false;
     long long bvh_prim_end_max = 0; bool bvh_bad = false;
     int bvh_depth = 0;                     // deepest leaf of the binary BVH (root = 0)
+    // multi-GPU (mgpu.cu): this context's NCCL communicator, if wgpt_comm_init / wgpt_group_create made one
+    void* nccl_comm = nullptr; int nccl_rank = 0, nccl_world = 1;
     std::string err;
 };
 
@@ -55,4 +58,6 @@ int fast_stats(wgpt_ctx* c, uint32_t out[8]);
 int fast_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]);
 int fast_trace_rays(wgpt_ctx* c, int n, const float* d_rays, const uint32_t* d_seeds, int* d_type, int* d_index, float* d_t);
 void fast_destroy(wgpt_ctx* c);
+// mgpu.cu
+void mgpu_destroy(wgpt_ctx* c);
 }

@@ -16,6 +16,7 @@ void launch_pinned_math(int fn, int n, const float* x, const float* y, float* ou
 // present.cu (K4)
 void launch_present(const float4* fb_in, float4* fb_clear, float4* rgba_out, uchar4* rgba8_out, uint32_t npix,
                     float frameNum, int clear, cudaStream_t stream);
+void launch_fix_alpha(float4* fb, uint32_t npix, cudaStream_t stream);
 void launch_fb_to_rgb(const float4* fb, float* rgb, uint32_t npix, cudaStream_t stream);
 void launch_quant_check(uint32_t first, uint32_t n, unsigned long long* out, cudaStream_t stream);
 void launch_accumulate(float4* fb, const float4* frame, uint32_t npix, int reset, cudaStream_t stream);

@@ -115,6 +115,14 @@ __global__ void __launch_bounds__(256) k_fb_to_rgb(const float4* __restrict__ fb
     }
 }
 
+// after a sum-reduce over shards the w lane counts the shards that rendered the pixel: back to the reference's 1.0
+__global__ void __launch_bounds__(256) k_fix_alpha(float4* __restrict__ fb, uint32_t npix) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        float* w = reinterpret_cast<float*>(&fb[i]) + 3;
+        if (*w != 0.0f && *w != 1.0f) *w = 1.0f;
+    }
+}
+
 static unsigned stream_grid(uint32_t n, unsigned threads) {
     unsigned blocks = (n + threads - 1) / threads;
     const unsigned cap = 148u * 8u;          // 148 SMs x 8 resident 256-thread CTAs
@@ -124,6 +132,10 @@ static unsigned stream_grid(uint32_t n, unsigned threads) {
 void launch_present(const float4* fb_in, float4* fb_clear, float4* rgba_out, uchar4* rgba8_out, uint32_t npix,
                     float frameNum, int clear, cudaStream_t stream) {
     k_present<<<stream_grid(npix, 256), 256, 0, stream>>>(fb_in, fb_clear, rgba_out, rgba8_out, npix, frameNum, clear);
+}
+
+void launch_fix_alpha(float4* fb, uint32_t npix, cudaStream_t stream) {
+    k_fix_alpha<<<stream_grid(npix, 256), 256, 0, stream>>>(fb, npix);
 }
 
 void launch_fb_to_rgb(const float4* fb, float* rgb, uint32_t npix, cudaStream_t stream) {
