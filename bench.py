@@ -32,6 +32,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# stdout carries exactly ONE JSON line: NCCL's banner (NCCL_DEBUG=VERSION / INFO print to stdout by default) goes to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 import numpy as np  # noqa: E402
 
@@ -285,7 +287,7 @@ def mgpu_self_check(dist, rank, world, local_rank):
     one.close()
     denom = np.maximum(np.abs(ref[:, :3]), 1e-6)
     return {"tile_bit_exact": bool(np.array_equal(ref.view(np.uint32), res["tiles"].view(np.uint32))),
-            "strata_max_rel": float(np.max(np.abs(res["strata"][:, :3] - ref[:, :3]) / denom)),
+            "strata_max_rel": float(np.nanmax(np.abs(res["strata"][:, :3] - ref[:, :3]) / denom)),
             "job": "C2 scene %dx%d, %d frames, %d ranks" % (W, H, frames, world)}
 
 

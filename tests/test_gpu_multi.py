@@ -62,11 +62,11 @@ def test_tile_shards_reduce_bit_exact(golden_meshes):
 def test_strata_shards_reduce_to_rounding(golden_meshes):
     scene, cam, want = scene_and_single(golden_meshes)
     got = run_group(scene, cam, 2, 1)
-    assert np.allclose(want, got, rtol=1e-5, atol=1e-6)
+    assert np.allclose(want, got, rtol=1e-5, atol=1e-6, equal_nan=True)
     assert (got[:, 3] == 1.0).all()
     if NGPU >= 4:
         got = run_group(scene, cam, 4, 2)        # 2 tile groups x 2 strata
-        assert np.allclose(want, got, rtol=1e-5, atol=1e-6)
+        assert np.allclose(want, got, rtol=1e-5, atol=1e-6, equal_nan=True)
 
 
 @pytest.mark.skipif(NGPU < 2, reason="needs >= 2 GPUs")
@@ -79,4 +79,4 @@ def test_one_process_per_gpu_reduce(tmp_path):
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     d = np.load(out)
     assert np.array_equal(bits(d["single"]), bits(d["tiles"]))
-    assert np.allclose(d["single"], d["strata"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(d["single"], d["strata"], rtol=1e-5, atol=1e-6, equal_nan=True)
