@@ -100,3 +100,31 @@ def test_dispatch_returns_before_the_frames_are_done(default_scene):
     e = setup(PathTracer(W, H, mode=MODE_FAST), scene, cam)
     e.render(1, N)
     assert np.array_equal(bits(e.read_framebuffer()), bits(got))
+
+
+def test_progressive_refresh_callback_and_pfm(default_scene, tmp_path):
+    """renderProgressive: dispatches between refreshes, `on_refresh` sees exactly what `fs` shows at that frame count
+    (the oracle presenting after the same number of frames); the .pfm file holds the float image."""
+    from webgpu_path_tracer_b200 import Renderer, Scene, Camera, imageio
+    scene = Scene()
+    cam = Camera()
+    cam.set_camera([0.5, 0, 2.5], [0.5, 0, 0], [0, 1, 0])
+    W, H = 96, 64
+    r = Renderer.create(mode=MODE_FAST)
+    r.initBuffers(scene, cam, W, H)
+    r.setRenderParameters({}, cam, W, H)
+    seen = []
+    r.renderProgressive(10, 4, lambda f, img: seen.append((f, img.copy())))
+    assert [f for f, _ in seen] == [4, 8, 10]
+    o = Oracle(W, H)
+    o.write_scene(scene.buffers())
+    done = 0
+    for f, img in seen:
+        o.write_uniforms(done + 1, 0, cam.viewMatrix)
+        o.render(done + 1, int(f) - done)
+        done = int(f)
+        o.write_uniforms(f, 0, cam.viewMatrix)
+        assert np.array_equal(bits(o.present()), bits(img.reshape(-1, 4)))
+    path = tmp_path / "hdr.pfm"
+    img = r.save_image(path)
+    assert np.array_equal(bits(imageio.read_pfm(path)), bits(img[:, :, :3]))

@@ -202,3 +202,14 @@ def test_napi_addon_source_passes_a_syntax_check_and_binds_only_declared_entry_p
                    "createShaderModule", "createComputePipeline", "createRenderPipeline", "createRenderPassDescriptor",
                    "computePass", "renderPass", "createBindGroup", "writeBuffer", "init"):
         assert re.search(r"\b%s\s*\(" % method, shim), method        # the call shapes renderer.js uses
+
+
+def test_pfm_round_trip(tmp_path):
+    from webgpu_path_tracer_b200 import imageio
+    rng = np.random.default_rng(0)
+    img = rng.uniform(0, 30, (5, 7, 4)).astype(np.float32)
+    img[0, 0, 0] = np.inf
+    p = tmp_path / "x.pfm"
+    imageio.write_pfm(p, img)
+    assert p.read_bytes().startswith(b"PF\n7 5\n-1.0\n")
+    assert np.array_equal(imageio.read_pfm(p), img[:, :, :3])

@@ -26,6 +26,7 @@ struct Session {
 
 struct FastState {
     Session sess;
+    unsigned acc_phase = 0;
     unsigned extend_blocks[2] = {0, 0};    // persistent extend grid on this context's device, without / with counters
     // wide BVH
     uint4* wide_nodes = nullptr; float4* wide_tris = nullptr; uint32_t* wide_scratch = nullptr;
@@ -53,6 +54,9 @@ struct FastState {
 };
 
 static const size_t PROF_QUADS = 2048;
+#ifndef WF_ACC_EVERY
+#define WF_ACC_EVERY 4
+#endif
 
 static void prof_fold(FastState* F) {
     if (!F->prof_used) return;
@@ -67,7 +71,7 @@ static void prof_fold(FastState* F) {
         cudaEventElapsedTime(&c2, F->prof_ev[4 * i + 2], F->prof_ev[4 * i + 3]);
         F->prof_ms[0] += a; F->prof_ms[1] += b; F->prof_ms[2] += c2;
         if (dump) fprintf(dump, "%.4f %.4f %.4f\n", a, b, c2);
-        F->prof_launches[0] += 1; F->prof_launches[1] += 1; F->prof_launches[2] += 2;
+        F->prof_launches[0] += 1; F->prof_launches[1] += 1; F->prof_launches[2] += 1;
     }
     if (dump) { fprintf(dump, "\n"); fclose(dump); }
     F->prof_used = 0;
@@ -274,10 +278,13 @@ int fast_pump(wgpt_ctx* c, int iterations) {
     S.uniforms = s.uniforms;                               // the view the session's frames were submitted with
     S.counters = s.counters_on ? c->d_counters : nullptr;
     const WideBvh WB = wide_view(c, F);
-    for (int i = 0; i < iterations; i++)
-        wf_launch_iteration(S, WB, s.P, (float4*)s.fb, s.reset_first, F->extend_blocks[S.counters ? 1 : 0], c->stream,
-                            c->stage_profiling ? prof_next(F) : nullptr);
-    c->last_launches += (uint64_t)iterations * WF_LAUNCHES_PER_ITERATION;
+    // the accumulate pass runs every WF_ACC_EVERY-th iteration and at the end of every pump: frames that complete in
+    // between wait in the staging ring (its window follows the frames FOLDED, so nothing is overwritten)
+    for (int i = 0; i < iterations; i++) {
+        const bool do_acc = i + 1 == iterations || (++F->acc_phase % WF_ACC_EVERY) == 0;
+        c->last_launches += (uint64_t)wf_launch_iteration(S, WB, s.P, (float4*)s.fb, s.reset_first, F->extend_blocks[S.counters ? 1 : 0],
+                                                          do_acc, c->stream, c->stage_profiling ? prof_next(F) : nullptr);
+    }
     return cuda_err(c, cudaGetLastError(), "wavefront iteration");
 }
 

@@ -47,7 +47,7 @@ __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
         for (uint32_t k = 0; k < WF_WORK_SHARDS; k++) { P.work_shards[16 * k] = 0ull; c->shard_lim[k] = wf_shard_count(c->work_limit, k); }
         c->n_extend = 0; c->extend_cursor = 0; c->n_next = 0;
         for (int k = 0; k < WF_MAX_RING; k++) c->done[k] = 0;
-        c->acc_k = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
+        c->acc_k = 0; c->acc_done = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
         c->finished = n_frames == 0 ? 1u : 0u; c->fallbacks = 0; c->iterations = 0;
         c->drain = 0; c->sparse = 0; c->live_read = 0; c->n_live = 0; c->n_live_next = 0; c->n_tie_blocks = 0;
     }
@@ -66,7 +66,7 @@ __global__ void k_wf_append(WfParams P, uint32_t more_frames) {
         WfControl* c = P.ctl;
         c->n_frames += more_frames;
         c->total_work += (unsigned long long)more_frames * P.items_per_frame;
-        const unsigned long long lim = (unsigned long long)(c->acc_k + P.ring) * P.items_per_frame;
+        const unsigned long long lim = (unsigned long long)(c->acc_done + P.ring) * P.items_per_frame;
         c->work_limit = lim < c->total_work ? lim : c->total_work;
         for (uint32_t k = 0; k < WF_WORK_SHARDS; k++) c->shard_lim[k] = wf_shard_count(c->work_limit, k);
         c->finished = 0; c->drain = 0; c->sparse = 0; c->n_live = 0; c->n_live_next = 0;
@@ -321,44 +321,61 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
     }
 }
 
-// after shade: publish the next ray queue, find frames that completed, advance the ring window
+// End of an iteration, after shade: publish the next ray queue, find the frames that completed, advance the ring window.
+// One warp; every lane reads what it needs up front (one round of loads instead of a chain of ~40 by one thread: this
+// launch sits between two big ones on the stream, its length is pure bubble).
+// (Measured and dropped: running this inside the shade launch, in the last block to leave it -- the arrival counter is one
+// more atomic per block on a single L2 address, 33 K per launch: shade +10..15 %, against ~2.5 us for this launch.)
 __global__ void k_wf_ctl_end(WfParams P) {
-    if (blockIdx.x != 0) return;
-    {   // the marks of this iteration have been consumed by the shade launch: clear them (one warp)
-        const uint32_t ntb = P.ctl->n_tie_blocks;
+    if (blockIdx.x != 0 || threadIdx.x >= 32) return;
+    const uint32_t lane = threadIdx.x;
+    WfControl* c = P.ctl;
+    const uint32_t ntb = c->n_tie_blocks, n_next = c->n_next, n_frames = c->n_frames, acc_done0 = c->acc_done;
+    const uint32_t drain0 = c->drain, n_live_next = c->n_live_next, live_read = c->live_read;
+    const unsigned long long total_work = c->total_work;
+    uint32_t acc_k = c->acc_k;
+    const unsigned long long dealt = lane < WF_WORK_SHARDS ? P.work_shards[16 * lane] : 0ull;
+    {   // the marks of this iteration have been consumed by the shade launch: clear them
         if (ntb <= WF_FRONT_BLOCKS) {
-            for (uint32_t i = threadIdx.x; i < ntb; i += blockDim.x) P.tie_bitmap[P.tie_blocks[i] >> 5] = 0u;
+            for (uint32_t i = lane; i < ntb; i += 32u) P.tie_bitmap[P.tie_blocks[i] >> 5] = 0u;
         } else {
             const uint32_t words = P.pool.capacity / WF_SHADE_THREADS / 32u + 1u;
-            for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) P.tie_bitmap[i] = 0u;
+            for (uint32_t i = lane; i < words; i += 32u) P.tie_bitmap[i] = 0u;
         }
-        __syncwarp();
     }
-    if (threadIdx.x != 0) return;
-    WfControl* c = P.ctl;
+    // frames whose every item finished (in frame order), 32 candidates per round; they are FOLDED by the accumulate pass,
+    // which the host launches behind this step every few iterations (P.do_acc): until then they wait in the staging ring
+    while (true) {
+        const uint32_t k = acc_k + lane;
+        const bool ok = k < n_frames && k - acc_done0 < P.ring && c->done[k % P.ring] == P.items_per_frame;
+        const uint32_t m = __ballot_sync(0xffffffffu, ok);
+        const uint32_t take = m == 0xffffffffu ? 32u : (uint32_t)__ffs((int)~m) - 1u;      // leading complete frames
+        if (lane < take) c->done[k % P.ring] = 0;
+        acc_k += take;
+        if (take < 32u) break;
+    }
+    const uint32_t acc_done = P.do_acc ? acc_k : acc_done0;
+    const unsigned long long lim = (unsigned long long)(acc_done + P.ring) * P.items_per_frame;
+    const unsigned long long work_limit = lim < total_work ? lim : total_work;
+    bool all = true;
+    if (lane < WF_WORK_SHARDS) {
+        c->shard_lim[lane] = wf_shard_count(work_limit, lane);
+        all = dealt >= wf_shard_count(total_work, lane);          // all work handed out <=> every shard has dealt its last item
+    }
+    all = __all_sync(0xffffffffu, all);
+    if (lane != 0) return;
     c->n_tie_blocks = 0;
-    c->n_extend = c->n_next; c->n_next = 0; c->extend_cursor = 0;
-    uint32_t n_ready = 0;
-    while (c->acc_k + n_ready < c->n_frames && n_ready < P.ring &&
-           c->done[(c->acc_k + n_ready) % P.ring] == P.items_per_frame) {
-        c->done[(c->acc_k + n_ready) % P.ring] = 0;
-        n_ready++;
-    }
-    c->ready_first = c->acc_k; c->n_ready = n_ready;
-    c->acc_k += n_ready;
-    unsigned long long lim = (unsigned long long)(c->acc_k + P.ring) * P.items_per_frame;
-    c->work_limit = lim < c->total_work ? lim : c->total_work;
-    for (uint32_t k = 0; k < WF_WORK_SHARDS; k++) c->shard_lim[k] = wf_shard_count(c->work_limit, k);
-    if (c->acc_k == c->n_frames) c->finished = 1;
+    c->n_extend = n_next; c->n_next = 0; c->extend_cursor = 0;
+    c->acc_k = acc_k;
+    if (P.do_acc) { c->ready_first = acc_done0; c->n_ready = acc_k - acc_done0; c->acc_done = acc_k; }
+    else c->n_ready = 0;
+    c->work_limit = work_limit;
+    if (acc_done == n_frames) c->finished = 1;
     // drain bookkeeping: the shade launch that just ran listed its live slots iff it saw drain == 1
-    c->n_live = c->n_live_next; c->n_live_next = 0;
-    if (c->drain) c->live_read ^= 1u;
-    c->sparse = (c->drain && (unsigned long long)c->n_live * WF_SPARSE_BELOW <= P.pool.capacity) ? 1u : 0u;
-    {   // all work handed out <=> every shard has dealt its last item
-        bool all = true;
-        for (uint32_t k = 0; k < WF_WORK_SHARDS; k++) all = all && P.work_shards[16 * k] >= wf_shard_count(c->total_work, k);
-        if (all) c->drain = 1;
-    }
+    c->n_live = n_live_next; c->n_live_next = 0;
+    if (drain0) c->live_read = live_read ^ 1u;
+    c->sparse = (drain0 && (unsigned long long)n_live_next * WF_SPARSE_BELOW <= P.pool.capacity) ? 1u : 0u;
+    if (all) c->drain = 1;
     c->iterations++;
 }
 
@@ -745,8 +762,10 @@ unsigned wf_extend_grid(bool counters) {
     return (unsigned)(sms * (per_sm > 0 ? per_sm : 1));
 }
 
-void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
-                         unsigned extend_blocks, cudaStream_t stream, cudaEvent_t* ev) {
+int wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P_in, float4* fb, int reset_first,
+                        unsigned extend_blocks, bool do_acc, cudaStream_t stream, cudaEvent_t* ev) {
+    WfParams P = P_in;
+    P.do_acc = do_acc ? 1 : 0;
     if (ev) cudaEventRecord(ev[0], stream);
     if (S.counters) k_wf_extend<true><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
@@ -761,11 +780,14 @@ void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams
     }
     if (ev) cudaEventRecord(ev[2], stream);
     k_wf_ctl_end<<<1, 32, 0, stream>>>(P);
-    const uint32_t npix = (uint32_t)S.W * (uint32_t)S.H;
-    unsigned acc_blocks = (npix + 255u) / 256u;
-    if (acc_blocks > 148u * 8u) acc_blocks = 148u * 8u;
-    k_wf_accumulate<<<acc_blocks, 256, 0, stream>>>(P, fb, npix, reset_first);
+    if (do_acc) {      // a whole-image launch even when no frame is ready: only every few iterations (fast.cu WF_ACC_EVERY)
+        const uint32_t npix = (uint32_t)S.W * (uint32_t)S.H;
+        unsigned acc_blocks = (npix + 255u) / 256u;
+        if (acc_blocks > 148u * 8u) acc_blocks = 148u * 8u;
+        k_wf_accumulate<<<acc_blocks, 256, 0, stream>>>(P, fb, npix, reset_first);
+    }
     if (ev) cudaEventRecord(ev[3], stream);
+    return do_acc ? 4 : 3;
 }
 
 // closest-hit hook over the wide BVH (wgpt_trace_rays in fast mode)

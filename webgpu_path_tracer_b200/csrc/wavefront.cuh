@@ -86,8 +86,10 @@ struct WfControl {
     uint32_t extend_cursor;            // persistent-warp fetch cursor
     uint32_t n_next;                   // rays compacted by shade for the next iteration
     uint32_t done[WF_MAX_RING];        // finished items per ring slot
-    uint32_t acc_k;                    // next frame ordinal to fold into binding 3
-    uint32_t ready_first, n_ready;     // frames the accumulate pass folds this iteration
+    uint32_t acc_k;                    // frames whose every item has finished (complete in the staging ring)
+    uint32_t acc_done;                 // frames folded into binding 3 (<= acc_k: the accumulate pass runs every few iterations);
+                                       // the ring window and `finished` follow THIS counter: a staging slot is free once folded
+    uint32_t ready_first, n_ready;     // frames the accumulate pass launched behind this control step folds (0: none launched)
     uint32_t n_frames;                 // frame ordinals to render in this call
     uint32_t finished;
     uint32_t fallbacks;                // rays re-traced with the reference-order walk
@@ -121,6 +123,7 @@ struct WfParams {
     double inv_items_per_frame;        // 1.0 / items_per_frame (quotient estimate, fixed up with integers)
     int bvh_depth;                     // deepest leaf of the binary BVH (bounds the reference's stack use)
     int frame0, frame_stride;          // frame number of ordinal k = frame0 + k * frame_stride
+    int do_acc;                        // the accumulate pass is launched right after this iteration's control step (set per launch)
     // optional probe outputs (first closest-hit query of every pixel), indexed by pixel
     int* prim_type; int* prim_index; float* prim_t;
 };
@@ -130,10 +133,10 @@ struct WfParams {
 void wf_launch_init(const WfParams& P, uint32_t n_frames, cudaStream_t stream);
 void wf_launch_append(const WfParams& P, uint32_t more_frames, cudaStream_t stream);
 unsigned wf_extend_grid(bool counters);      // CTAs of the persistent extend grid on the current device
-// ev: optional 4 events recorded before extend, after extend, after shade, after accumulate
-void wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
-                         unsigned extend_blocks, cudaStream_t stream, cudaEvent_t* ev = nullptr);
-#define WF_LAUNCHES_PER_ITERATION 4
+// ev: optional 4 events recorded before extend, after extend, after shade, after control (+ accumulate)
+// do_acc: also launch the accumulate pass (frames complete since the last one are folded); returns the launches issued
+int wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams& P, float4* fb, int reset_first,
+                        unsigned extend_blocks, bool do_acc, cudaStream_t stream, cudaEvent_t* ev = nullptr);
 void launch_trace_rays_wide(const DeviceScene& S, const WideBvh& WB, int n, const float* rays, const uint32_t* seeds,
                             int* out_type, int* out_index, float* out_t, uint32_t* fallbacks, cudaStream_t stream);
 

@@ -65,3 +65,22 @@ def decode_png(data):
     raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + w * ch)
     assert not raw[:, 0].any()
     return raw[:, 1:].reshape(h, w, ch)
+
+
+def write_pfm(path, image):
+    """HDR output of the f32 present (or of binding 3 itself): Portable Float Map, little-endian RGB float32, rows
+    bottom-to-top (the format's convention).  `image`: (H, W, 3) or (H, W, 4) floats."""
+    a = np.asarray(image, np.float32)
+    h, w = a.shape[:2]
+    with open(path, "wb") as f:
+        f.write(b"PF\n%d %d\n-1.0\n" % (w, h))
+        f.write(np.ascontiguousarray(a[::-1, :, :3]).astype("<f4").tobytes())
+
+
+def read_pfm(path):
+    with open(path, "rb") as f:
+        assert f.readline().strip() == b"PF"
+        w, h = (int(x) for x in f.readline().split())
+        scale = float(f.readline())
+        data = np.frombuffer(f.read(), "<f4" if scale < 0 else ">f4").reshape(h, w, 3)
+    return data[::-1].astype(np.float32)

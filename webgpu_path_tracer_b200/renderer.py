@@ -72,12 +72,31 @@ class Renderer:
         self.webGPU.render(first, int(n_frames))
         self.frameNum += n_frames
 
+    def renderProgressive(self, n_frames, refresh_every, on_refresh):
+        """The progressive viewer loop of renderAnimation (renderer.js:163-214: the canvas refreshes while samples
+        accumulate) without a canvas: frames are dispatched one by one -- wgpt_dispatch enqueues and returns, the frames
+        join one living wavefront -- and every `refresh_every` frames `on_refresh(frameNum, image)` receives what `fs`
+        would show (float RGBA, H x W x 4).  Returns the last image."""
+        img = None
+        for k in range(int(n_frames)):
+            self.renderAnimation(present=False)
+            if (k + 1) % int(refresh_every) == 0 or k + 1 == int(n_frames):
+                img = self.webGPU.present().reshape(self.HEIGHT, self.WIDTH, 4)
+                self.last_image = img
+                if on_refresh is not None:
+                    on_refresh(self.frameNum, img)
+        return img
+
     def present(self, rgba8=False):
         self.webGPU.write_uniforms(self.frameNum, 0, self.camera.viewMatrix)
         return self.webGPU.present(rgba8=rgba8)
 
     def save_image(self, path):
-        """Write what the canvas would show (fs output, RGBA8) to a .png or .ppm file."""
+        """Write what the canvas would show (fs output, RGBA8) to a .png or .ppm file; .pfm gets the float image."""
+        if str(path).lower().endswith(".pfm"):
+            img = np.asarray(self.present()).reshape(self.HEIGHT, self.WIDTH, 4)
+            imageio.write_pfm(path, img)
+            return img
         rgba8 = np.asarray(self.present(rgba8="only")).reshape(self.HEIGHT, self.WIDTH, 4)
         (imageio.write_ppm if str(path).lower().endswith(".ppm") else imageio.write_png)(path, rgba8)
         return rgba8
