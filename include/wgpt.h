@@ -114,6 +114,16 @@ int wgpt_render(wgpt_ctx* ctx, int first_frame, int n_frames);
  * clears binding 3 when uniforms.resetBuffer == 1.  rgba_out: host, 4 floats per pixel;
  * rgba8_out (optional, may be NULL): host, 4 bytes per pixel, round(c*255). */
 int wgpt_present(wgpt_ctx* ctx, float* rgba_out, uint8_t* rgba8_out);
+/* Bytes-only present that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same kernel and the same bytes as wgpt_present(ctx, NULL, rgba8_out) -- wgpt_present cudaMallocs its
+ * device staging on every call -- but the RGBA8 image is staged in a static device array of
+ * WGPT_STATIC_PRESENT_MAX_PIXELS x 4 bytes (8 MiB) that every GPU that loads the library holds until exit.  Images with
+ * more pixels are rejected with WGPT_E_INVALID.  Every call on a device shares that array (it keeps the last call's
+ * bytes; each call overwrites what it reads back), so calls that OVERLAP on the GPU -- two contexts of one device, two
+ * host threads -- race: serialise them.  Calls no cudaMalloc / cudaFree / allocating library routine. */
+#define WGPT_STATIC_PRESENT_MAX_PIXELS (2u << 20)
+int wgpt_present_rgba8_static(wgpt_ctx* ctx, uint8_t* rgba8_out);
 
 /* ---- parity hooks (no reference counterpart) ---- */
 /* Re-runs one dispatch with the current uniforms WITHOUT touching binding 3 and returns, per

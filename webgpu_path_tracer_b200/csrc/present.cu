@@ -147,3 +147,55 @@ void launch_accumulate(float4* fb, const float4* frame, uint32_t npix, int reset
 }
 
 }  // namespace wg
+
+// ---------------------------------------------------------------------------------------------------------------
+// wgpt_present_rgba8_static -- the bytes-only present WITHOUT any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight
+// serving loops, harnesses that forbid it).  wgpt_present cudaMallocs its device staging on every call; this variant
+// stages the RGBA8 image in a file-scope device array of WGPT_STATIC_PRESENT_MAX_PIXELS x 4 bytes (8 MiB), which every
+// GPU that loads the library holds until exit.
+//   * In HOST code the array's name is a host-side stand-in, not a device address: its device address is looked up once
+//     per device, with that device current, by cudaGetSymbolAddress, and THAT pointer goes to the kernel.
+//   * Every call on a device shares the array and it keeps the last call's contents; the kernel overwrites all 4 x npix
+//     bytes it then copies out, so nothing has to start at zero.  Calls that overlap on the GPU (two contexts of one
+//     device on their own streams, two host threads) RACE on it: serialise them.
+//   * Same kernel, same bytes as wgpt_present(ctx, NULL, rgba8_out), including the clear of binding 3 when
+//     uniforms.resetBuffer == 1 (fragment.js:30-33).
+#include <string>
+#include "context.h"
+
+// WGPT_STATIC_PRESENT_MAX_PIXELS = 2 Mi pixels (include/wgpt.h): 1920 x 1080 fits (2,073,600)
+static __device__ __align__(256) unsigned char g_static_present_rgba8[(size_t)WGPT_STATIC_PRESENT_MAX_PIXELS * 4];
+
+#define WGPT_STATIC_MAX_DEVICES 64
+static uchar4* g_static_present_ptr[WGPT_STATIC_MAX_DEVICES];      // device address of the array, per device ordinal
+
+extern "C" int wgpt_present_rgba8_static(wgpt_ctx* c, uint8_t* rgba8_out) {
+    if (!c || !rgba8_out) return WGPT_E_INVALID;
+    if (!c->have_uniforms) return wg::set_err(c, WGPT_E_STATE, "uniforms (binding 0) not written");
+    const uint32_t npix = (uint32_t)c->cfg.width * (uint32_t)c->cfg.height;
+    if (npix > WGPT_STATIC_PRESENT_MAX_PIXELS)
+        return wg::set_err(c, WGPT_E_INVALID, "wgpt_present_rgba8_static: image has " + std::to_string(npix) +
+                           " pixels, the static staging array holds at most " + std::to_string(WGPT_STATIC_PRESENT_MAX_PIXELS) +
+                           " (use wgpt_present)");
+    const int dev = c->cfg.device;
+    if (dev < 0 || dev >= WGPT_STATIC_MAX_DEVICES) return wg::set_err(c, WGPT_E_INVALID, "wgpt_present_rgba8_static: device ordinal >= 64");
+    cudaError_t e = cudaSetDevice(dev);
+    if (e != cudaSuccess) return wg::cuda_err(c, e, "present_rgba8_static");
+    if (!g_static_present_ptr[dev]) {                      // set-up, once per device, with that device current
+        void* p = nullptr;
+        if ((e = cudaGetSymbolAddress(&p, g_static_present_rgba8)) != cudaSuccess) return wg::cuda_err(c, e, "cudaGetSymbolAddress(static present staging)");
+        g_static_present_ptr[dev] = (uchar4*)p;
+    }
+    uchar4* d_rgba8 = g_static_present_ptr[dev];
+    {   // `fs` runs after the compute passes submitted before it (launches only: the wavefront pool exists already)
+        const int rc = wg::fast_flush(c);
+        if (rc) return rc;
+    }
+    const int clear = c->uniforms.resetBuffer == 1.0f;
+    wg::launch_present((const float4*)c->dbuf[3], (float4*)c->dbuf[3], nullptr, d_rgba8, npix, c->uniforms.frameNum, clear, c->stream);
+    if ((e = cudaGetLastError()) != cudaSuccess) return wg::cuda_err(c, e, "present_rgba8_static");
+    if ((e = cudaMemcpyAsync(rgba8_out, d_rgba8, (size_t)npix * 4, cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess)
+        return wg::cuda_err(c, e, "present_rgba8_static");
+    return wg::cuda_err(c, cudaStreamSynchronize(c->stream), "present_rgba8_static");
+}
