@@ -453,11 +453,15 @@ def main():
              "algorithmic_bytes_per_launch": alg_bytes_rank * args.steps / n, "avg_launch_ms": ms / n, "launches": n,
              "share_of_step": ms / sum(step_ms), "traffic": None}
         k = cap.get(key)
-        if k:
+        if k and k.get("algorithmic_bytes"):
             # same-launch pair: DRAM bytes ncu measured for the captured launch vs the algorithmic bytes of THAT launch
             r["traffic"] = k["dram_bytes"]
             r["traffic_launch"] = {"dram_bytes": k["dram_bytes"], "algorithmic_bytes": k["algorithmic_bytes"], "ms": k["ms"],
-                                   "ratio": k["dram_bytes"] / k["algorithmic_bytes"], "what": k.get("what")}
+                                   "ratio": k["dram_bytes"] / k["algorithmic_bytes"], "what": k.get("what"),
+                                   "physical_dram_GBps": k["dram_bytes"] / (k["ms"] * 1e-3) / 1e9,
+                                   "physical_dram_frac_of_peak": k["dram_bytes"] / (k["ms"] * 1e-3) / 1e9 / peak,
+                                   "l1_hit_pct": k.get("l1_hit_pct"), "l2_hit_pct": k.get("l2_hit_pct"),
+                                   "warps_active_pct": k.get("warps_active_pct")}
             if k.get("warp_inst_per_unit"):
                 units = rays_rank
                 inst_s = k["warp_inst_per_unit"] * units * args.steps / (ms * 1e-3)

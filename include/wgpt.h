@@ -161,6 +161,9 @@ int wgpt_fast_statistics(wgpt_ctx* ctx, wgpt_fast_stats* out);
  * wgpt_stage_timings synchronises and returns the sums since it was last called:
  * ms[0] extend (K3 traversal), ms[1] shade, ms[2] control + accumulate (K4), ms[3] hierarchy build (K5 BVH build + K2 wide flatten);
  * launches[i] = kernel launches counted in ms[i]. */
+/* measurement: rays the extend stage traced in iteration i (i < 64) of the last render -- what an ncu capture of launch i
+ * processed (bench.py's same-launch traffic / instructions-per-ray figures, tools/evidence_collect.py) */
+int wgpt_extend_history(wgpt_ctx* ctx, uint32_t out[64]);
 int wgpt_set_stage_profiling(wgpt_ctx* ctx, int enabled);
 int wgpt_stage_timings(wgpt_ctx* ctx, float ms[4], uint64_t launches[4]);
 

@@ -14,3 +14,6 @@ pt.write_uniforms(1, 0, cam.viewMatrix)
 pt.render(1, frames)
 ms, launches = pt.last_timing()
 print("%s %d frames: %.3f ms/frame, %.1f Msamples/s, launches=%d" % (cfg, frames, ms / frames, W * H * kw.get("num_samples", 1) * frames / ms / 1e3, launches))
+import json
+json.dump({"config": cfg, "frames": frames, "n_extend": [int(x) for x in pt.extend_history()], "pool_slots": pt.fast_statistics()["pool_slots"]},
+          open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out", "prof_hist_%s.json" % cfg), "w"))

@@ -20,7 +20,7 @@ EXPORTS = ("wgpt_default_config", "wgpt_create", "wgpt_destroy", "wgpt_last_erro
            "wgpt_read_buffer", "wgpt_device_ptr", "wgpt_dispatch", "wgpt_render", "wgpt_present", "wgpt_probe",
            "wgpt_trace_rays", "wgpt_counters", "wgpt_set_counters", "wgpt_last_timing", "wgpt_synchronize",
            "wgpt_pinned_math", "wgpt_fast_statistics", "wgpt_set_stage_profiling", "wgpt_stage_timings", "wgpt_k4_timing", "wgpt_present_quant_check",
-           "wgpt_timer_mark", "wgpt_timer_elapsed", "wgpt_present_rgba8_static", "wgpt_nccl_unique_id", "wgpt_comm_init", "wgpt_reduce_framebuffer", "wgpt_group_create", "wgpt_group_destroy",
+           "wgpt_timer_mark", "wgpt_timer_elapsed", "wgpt_extend_history", "wgpt_present_rgba8_static", "wgpt_nccl_unique_id", "wgpt_comm_init", "wgpt_reduce_framebuffer", "wgpt_group_create", "wgpt_group_destroy",
            "wgpt_group_last_error", "wgpt_group_size", "wgpt_group_ctx", "wgpt_group_write_buffer", "wgpt_group_render",
            "wgpt_group_reduce")
 
@@ -86,6 +86,7 @@ def load_library(path=None):
     L.wgpt_set_stage_profiling.argtypes = [vp, i32]
     L.wgpt_stage_timings.argtypes = [vp, C.POINTER(C.c_float * 4), C.POINTER(C.c_uint64 * 4)]
     L.wgpt_present_rgba8_static.argtypes = [vp, vp]
+    L.wgpt_extend_history.argtypes = [vp, vp]
     L.wgpt_timer_mark.argtypes = [vp, i32]
     L.wgpt_timer_elapsed.argtypes = [vp, C.POINTER(C.c_float)]
     L.wgpt_nccl_unique_id.argtypes = [vp]
@@ -215,6 +216,11 @@ class PathTracer:
         out8 = np.empty((self.H * self.W, 4), np.uint8)
         self._ck(self.L.wgpt_present_rgba8_static(self.h, _p(out8)), "wgpt_present_rgba8_static")
         return out8
+
+    def extend_history(self):
+        out = np.zeros(64, np.uint32)
+        self._ck(self.L.wgpt_extend_history(self.h, _p(out)), "wgpt_extend_history")
+        return out
 
     def synchronize(self):
         self._ck(self.L.wgpt_synchronize(self.h), "wgpt_synchronize")

@@ -230,6 +230,12 @@ int wgpt_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]) {
     return fast_stage_timings(c, ms, launches);
 }
 
+int wgpt_extend_history(wgpt_ctx* c, uint32_t out[64]) {
+    if (!c || !out) return WGPT_E_INVALID;
+    cudaSetDevice(c->cfg.device);
+    return fast_extend_history(c, out);
+}
+
 int wgpt_synchronize(wgpt_ctx* c) {
     if (!c) return WGPT_E_INVALID;
     cudaSetDevice(c->cfg.device);

@@ -56,6 +56,7 @@ int fast_close(wgpt_ctx* c);                                      // flush, and 
 int fast_render_probe(wgpt_ctx* c, int first_frame, int n_frames, int reset_first, int* d_ptype, int* d_pindex, float* d_pt);
 int fast_stats(wgpt_ctx* c, uint32_t out[8]);
 int fast_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]);
+int fast_extend_history(wgpt_ctx* c, uint32_t out[64]);
 int fast_trace_rays(wgpt_ctx* c, int n, const float* d_rays, const uint32_t* d_seeds, int* d_type, int* d_index, float* d_t);
 void fast_destroy(wgpt_ctx* c);
 // mgpu.cu

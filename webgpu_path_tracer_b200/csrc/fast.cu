@@ -411,6 +411,17 @@ int fast_stats(wgpt_ctx* c, uint32_t out[8]) {
     return WGPT_OK;
 }
 
+// rays the extend stage traced in iteration i (i < 64) of the last session: what an ncu capture of launch i processed
+int fast_extend_history(wgpt_ctx* c, uint32_t out[64]) {
+    memset(out, 0, 64 * sizeof(uint32_t));
+    FastState* F = c->fast;
+    if (!F || !F->pool_ready) return WGPT_OK;
+    int rc = fast_flush(c);
+    if (rc) return rc;
+    cudaStreamSynchronize(c->stream);
+    return cuda_err(c, cudaMemcpy(out, F->P.ctl->hist_n_extend, 64 * sizeof(uint32_t), cudaMemcpyDeviceToHost), "extend_history");
+}
+
 int fast_stage_timings(wgpt_ctx* c, float ms[4], uint64_t launches[4]) {
     for (int i = 0; i < 4; i++) { ms[i] = 0.0f; launches[i] = 0; }
     FastState* F = c->fast;

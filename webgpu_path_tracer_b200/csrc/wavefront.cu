@@ -50,6 +50,7 @@ __global__ void k_wf_init(WfParams P, uint32_t n_frames) {
         c->acc_k = 0; c->acc_done = 0; c->ready_first = 0; c->n_ready = 0; c->n_frames = n_frames;
         c->finished = n_frames == 0 ? 1u : 0u; c->fallbacks = 0; c->iterations = 0;
         c->drain = 0; c->sparse = 0; c->live_read = 0; c->n_live = 0; c->n_live_next = 0; c->n_tie_blocks = 0;
+        for (int k = 0; k < 64; k++) c->hist_n_extend[k] = 0;
     }
 }
 
@@ -366,6 +367,7 @@ __global__ void k_wf_ctl_end(WfParams P) {
     if (lane != 0) return;
     c->n_tie_blocks = 0;
     c->n_extend = n_next; c->n_next = 0; c->extend_cursor = 0;
+    if (c->iterations + 1u < 64u) c->hist_n_extend[c->iterations + 1u] = n_next;
     c->acc_k = acc_k;
     if (P.do_acc) { c->ready_first = acc_done0; c->n_ready = acc_k - acc_done0; c->acc_done = acc_k; }
     else c->n_ready = 0;

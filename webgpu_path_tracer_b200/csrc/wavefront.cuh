@@ -103,6 +103,7 @@ struct WfControl {
     uint32_t n_live, n_live_next;
     unsigned long long shard_lim[WF_WORK_SHARDS];   // wf_shard_count(work_limit, c), refreshed with work_limit
     uint32_t n_tie_blocks;             // shade blocks that hold a slot the extend stage marked (tie / stack overflow) this iteration
+    uint32_t hist_n_extend[64];        // rays queued for the extend stage of iteration i (i < 64) of the session: measurement only
 };
 
 struct WfParams {
