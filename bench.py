@@ -32,8 +32,17 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# stdout carries exactly ONE JSON line: NCCL's banner (NCCL_DEBUG=VERSION / INFO print to stdout by default) goes to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout carries exactly ONE JSON line.  Libraries print there too (NCCL's version banner under NCCL_DEBUG=VERSION / INFO),
+# so file descriptor 1 is pointed at stderr for the whole run and the line goes to a saved copy of the real stdout.
+sys.stdout.flush()
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line):
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
 
 import numpy as np  # noqa: E402
 
@@ -182,7 +191,7 @@ def run_reference(args):
             "e2e": {"value": value, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "reference WebGPU path unavailable on this box (no graphics stack / JS engine); this is the CPU oracle"}
-    print(json.dumps(line))
+    emit(line)
 
 
 def quick_config(cfg_name, frames, device):
@@ -536,7 +545,7 @@ def main():
             "other_configs": other, "per_frame": per_frame, "mgpu_check": mgpu_check,
             "rank0_last_render_ms": render_ms,
             "fast_stats": fstats}
-    print(json.dumps(line))
+    emit(line)
     if dist:
         dist.barrier()
         dist.destroy_process_group()

@@ -118,7 +118,9 @@ int wgpt_comm_init(wgpt_ctx* c, const void* id128, int rank, int world) {
     return WGPT_OK;
 }
 
-int wgpt_reduce_framebuffer(wgpt_ctx* c, int root) {
+// fix_alpha: launch the w-lane fix behind the reduce (false inside ncclGroupStart / End, where the reduce itself is only
+// issued at GroupEnd: the caller launches the fix afterwards)
+static int reduce_framebuffer(wgpt_ctx* c, int root, bool fix_alpha) {
     if (!c) return WGPT_E_INVALID;
     if (!c->nccl_comm) return set_err(c, WGPT_E_STATE, "wgpt_comm_init has not been called on this context");
     if (root < -1 || root >= c->nccl_world) return set_err(c, WGPT_E_INVALID, "root out of range (-1 = all ranks get the sum)");
@@ -131,9 +133,11 @@ int wgpt_reduce_framebuffer(wgpt_ctx* c, int root) {
     else rc = nccl()->Reduce(c->dbuf[3], c->dbuf[3], n, kNcclFloat32, kNcclSum, root, (NcclComm)c->nccl_comm, c->stream);
     if (rc) return nccl_err(c, rc, "ncclReduce(binding 3)");
     // the w lane now counts the shards that rendered the pixel: back to the reference's 1.0 where the sum landed
-    if (root < 0 || root == c->nccl_rank) launch_fix_alpha((float4*)c->dbuf[3], (uint32_t)(c->dbytes[3] / 16), c->stream);
+    if (fix_alpha && (root < 0 || root == c->nccl_rank)) launch_fix_alpha((float4*)c->dbuf[3], (uint32_t)(c->dbytes[3] / 16), c->stream);
     return cuda_err(c, cudaGetLastError(), "reduce_framebuffer");
 }
+
+int wgpt_reduce_framebuffer(wgpt_ctx* c, int root) { return reduce_framebuffer(c, root, true); }
 
 }  // extern "C"
 
@@ -224,10 +228,14 @@ int wgpt_group_reduce(wgpt_group* g, int root) {
     int rc = WGPT_OK;
     if (g->ctx.size() > 1) {
         nccl()->GroupStart();
-        for (size_t r = 0; r < g->ctx.size() && rc == WGPT_OK; r++) rc = wgpt_reduce_framebuffer(g->ctx[r], root);
+        for (size_t r = 0; r < g->ctx.size() && rc == WGPT_OK; r++) rc = reduce_framebuffer(g->ctx[r], root, false);
         const int ge = nccl()->GroupEnd();
         if (rc == WGPT_OK && ge) rc = nccl_err(g->ctx[root], ge, "ncclGroupEnd");
         if (rc) { g->err = wgpt_last_error(g->ctx[root]); return rc; }
+        // the reduces were issued at GroupEnd: NOW the w lane can go back to 1.0 behind root's reduce
+        wgpt_ctx* rc_ctx = g->ctx[root];
+        cudaSetDevice(rc_ctx->cfg.device);
+        launch_fix_alpha((float4*)rc_ctx->dbuf[3], (uint32_t)(rc_ctx->dbytes[3] / 16), rc_ctx->stream);
     }
     return for_each_ctx(g, [&](int r) { return wgpt_synchronize(g->ctx[r]); });
 }

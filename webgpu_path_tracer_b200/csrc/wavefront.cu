@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(128, WF_EXTEND_MINB) k_wf_extend(DeviceScene S
                 if (!ambiguous) reinterpret_cast<float*>(&P.pool.x[slot])[2] = closest;
                 reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = (tag0 & ~0xf0u) | ((uint32_t)(ambiguous ? WF_CLS_OVERFLOW : WF_CLS_TIE) << 4);
                 {   // note the shade block of this slot (first marker of a block appends it to the front list)
-                    const uint32_t blk = slot / WF_SHADE_THREADS, bit = 1u << (blk & 31u);
+                    const uint32_t blk = slot / P.shade_threads, bit = 1u << (blk & 31u);
                     if (!(atomicOr(&P.tie_bitmap[blk >> 5], bit) & bit)) {
                         const uint32_t at = atomicAdd(&ctl->n_tie_blocks, 1u);
                         if (at < WF_FRONT_BLOCKS) P.tie_blocks[at] = blk;
@@ -390,23 +390,26 @@ __device__ __forceinline__ void start_sample(const DeviceScene& S, uint32_t pixe
     ray = sample_ray(S, ps, si, sj, rng);
 }
 
+#ifndef WF_SHADE_THREADS_MIXED
+#define WF_SHADE_THREADS_MIXED 512     // shade block of scenes with several shade classes (WfParams::shade_threads)
+#endif
 #ifndef WF_SHADE_MINB
 #define WF_SHADE_MINB 4
 #endif
 // SPEC: what the launcher knows about the scene, so that code the scene cannot reach is not in the kernel at all
 // (the generic kernel is 170 KB of instructions; 9 % of its issue stalls were instruction fetches): -1 = nothing
 // (everything decided at run time), else bit 0 = binding 1 holds spheres, bit 1 = IMPORTANCE_SAMPLING is on.
-template <bool COUNT, int SPEC>
-__global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(DeviceScene S, WfParams P) {
+template <bool COUNT, int SPEC, int THREADS>
+__global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_shade(DeviceScene S, WfParams P) {
     constexpr bool SPH = SPEC < 0 || (SPEC & 1) != 0;
     constexpr int IS = SPEC < 0 ? -1 : ((SPEC >> 1) & 1);
     __shared__ uint32_t s_done[WF_MAX_RING];
     __shared__ uint32_t s_key_cnt[32];                 // slots per shade key
-    __shared__ float4 s_x[WF_SHADE_THREADS];            // (tag, hit index, u, v) of the block's slots
-    __shared__ uint32_t s_perm[WF_SHADE_THREADS];
-    __shared__ uint32_t s_q[WF_SHADE_THREADS];          // slot ids for the next ray queue
-    __shared__ uint32_t s_slot[WF_SHADE_THREADS];       // sparse launches: the slot of list entry (block base + i)
-    __shared__ uint32_t s_live[WF_SHADE_THREADS];       // drain phase: slot ids for the next live list
+    __shared__ float4 s_x[THREADS];            // (tag, hit index, u, v) of the block's slots
+    __shared__ uint32_t s_perm[THREADS];
+    __shared__ uint32_t s_q[THREADS];          // slot ids for the next ray queue
+    __shared__ uint32_t s_slot[THREADS];       // sparse launches: the slot of list entry (block base + i)
+    __shared__ uint32_t s_live[THREADS];       // drain phase: slot ids for the next live list
     __shared__ uint32_t s_qn, s_arrived, s_ln;
     WfControl* ctl = P.ctl;
     if (ctl->finished) return;                             // the host notices the flag one batch late: those launches are empty
@@ -690,7 +693,7 @@ __global__ void __launch_bounds__(WF_SHADE_THREADS, WF_SHADE_MINB) k_wf_shade(De
         }
         __syncwarp();
         uint32_t last = 0;
-        if (lane == 0) { __threadfence_block(); last = atomicAdd(&s_arrived, 1u) == WF_SHADE_THREADS / 32 - 1 ? 1u : 0u; }
+        if (lane == 0) { __threadfence_block(); last = atomicAdd(&s_arrived, 1u) == THREADS / 32 - 1 ? 1u : 0u; }
         last = __shfl_sync(0xffffffffu, last, 0);
         if (last) {
             __threadfence_block();
@@ -768,17 +771,20 @@ int wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams&
                         unsigned extend_blocks, bool do_acc, cudaStream_t stream, cudaEvent_t* ev) {
     WfParams P = P_in;
     P.do_acc = do_acc ? 1 : 0;
+    P.shade_threads = (!S.counters && (S.NUM_SPHERES > 0 || S.K.IMPORTANCE_SAMPLING)) ? WF_SHADE_THREADS_MIXED : 256u;
     if (ev) cudaEventRecord(ev[0], stream);
     if (S.counters) k_wf_extend<true><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     else k_wf_extend<false><<<extend_blocks, 128, 0, stream>>>(S, WB, P);
     if (ev) cudaEventRecord(ev[1], stream);
-    const unsigned shade_blocks = (P.pool.capacity + WF_SHADE_THREADS - 1u) / WF_SHADE_THREADS + WF_FRONT_BLOCKS;
-    if (S.counters) k_wf_shade<true, -1><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P);
-    else switch ((S.NUM_SPHERES > 0 ? 1 : 0) | (S.K.IMPORTANCE_SAMPLING ? 2 : 0)) {
-        case 0: k_wf_shade<false, 0><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P); break;
-        case 1: k_wf_shade<false, 1><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P); break;
-        case 2: k_wf_shade<false, 2><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P); break;
-        default: k_wf_shade<false, 3><<<shade_blocks, WF_SHADE_THREADS, 0, stream>>>(S, P); break;
+    const int spec = (S.NUM_SPHERES > 0 ? 1 : 0) | (S.K.IMPORTANCE_SAMPLING ? 2 : 0);
+    const unsigned st = P.shade_threads;
+    const unsigned shade_blocks = (P.pool.capacity + st - 1u) / st + WF_FRONT_BLOCKS;
+    if (S.counters) k_wf_shade<true, -1, 256><<<shade_blocks, 256, 0, stream>>>(S, P);
+    else switch (spec) {
+        case 0: k_wf_shade<false, 0, 256><<<shade_blocks, 256, 0, stream>>>(S, P); break;
+        case 1: k_wf_shade<false, 1, WF_SHADE_THREADS_MIXED><<<shade_blocks, WF_SHADE_THREADS_MIXED, 0, stream>>>(S, P); break;
+        case 2: k_wf_shade<false, 2, WF_SHADE_THREADS_MIXED><<<shade_blocks, WF_SHADE_THREADS_MIXED, 0, stream>>>(S, P); break;
+        default: k_wf_shade<false, 3, WF_SHADE_THREADS_MIXED><<<shade_blocks, WF_SHADE_THREADS_MIXED, 0, stream>>>(S, P); break;
     }
     if (ev) cudaEventRecord(ev[2], stream);
     k_wf_ctl_end<<<1, 32, 0, stream>>>(P);

@@ -12,7 +12,7 @@ namespace wg {
 
 #define WF_MAX_RING 256
 #ifndef WF_SHADE_THREADS
-#define WF_SHADE_THREADS 256     // slots per shade block
+#define WF_SHADE_THREADS 256     // slots per shade block (the smaller of the two block sizes: sizes bitmaps)
 #endif
 #ifndef WF_FRONT_BLOCKS
 #define WF_FRONT_BLOCKS 512      // leading shade blocks that take over the blocks holding marked slots
@@ -124,6 +124,11 @@ struct WfParams {
     double inv_items_per_frame;        // 1.0 / items_per_frame (quotient estimate, fixed up with integers)
     int bvh_depth;                     // deepest leaf of the binary BVH (bounds the reference's stack use)
     int frame0, frame_stride;          // frame number of ordinal k = frame0 + k * frame_stride
+    // Slots per shade block of THIS launch: 256, or 512 for scenes with several shade classes in flight (spheres in
+    // binding 1, or IMPORTANCE_SAMPLING on): the block-local material sort then leaves fewer mixed warps (shade C1 -12 %,
+    // C3 -9 %); single-material scenes gain nothing from the sort and pay the heavier block (C4 +11 %), so they keep 256.
+    // The extend stage marks tie / overflow slots per shade block, so it needs the same number.
+    uint32_t shade_threads;
     int do_acc;                        // the accumulate pass is launched right after this iteration's control step (set per launch)
     // optional probe outputs (first closest-hit query of every pixel), indexed by pixel
     int* prim_type; int* prim_index; float* prim_t;
