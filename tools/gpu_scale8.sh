@@ -14,9 +14,6 @@ print('$name', round(d['value'],1), 'e2e', round(d['e2e']['value'],1), 'ms/step'
 }
 run bench_mg8_r02 8 --steps 3 --warmup 2
 run bench_mg8_tiles1 8 --steps 3 --warmup 2 --tiles 1 --no-extras
-run bench_mg8_tiles8 8 --steps 3 --warmup 2 --tiles 8 --no-extras
 run bench_mg8_tiles2 8 --steps 3 --warmup 2 --tiles 2 --no-extras
 run bench_mg4_r02 4 --steps 3 --warmup 2 --no-extras
-run bench_mg2_r02 2 --steps 2 --warmup 2 --no-extras
 run bench_C3_mg8_r02 8 --config C3 --steps 3 --warmup 2 --no-extras
-run bench_C5_mg8_r02 8 --config C5 --steps 1 --warmup 1 --no-extras
