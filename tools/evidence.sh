@@ -16,6 +16,10 @@ done
 python tools/evidence_collect.py $R --traffic-only > $O/traffic_collect.log 2>&1; echo "traffic rc=$?"; cp profiles/traffic.json $O/traffic.json
 timeout 900 python bench.py --steps 3 --warmup 3 > $O/bench_$R.json 2> $O/bench_err.log; echo "bench rc=$?"
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref_$R.json 2>> $O/bench_err.log; echo "bench ref rc=$?"
+timeout 200 python bench.py --config C1 --steps 5 --warmup 3 --no-extras --cpu-baseline-frames 8 > $O/bench_C1_$R.json 2>> $O/bench_err.log
+timeout 200 python bench.py --config C2 --steps 5 --warmup 3 --no-extras --cpu-baseline-frames 8 > $O/bench_C2_$R.json 2>> $O/bench_err.log
+timeout 300 python bench.py --config C3 --steps 3 --warmup 3 --no-extras --cpu-baseline-frames 4 > $O/bench_C3_$R.json 2>> $O/bench_err.log
+timeout 600 python bench.py --config C5 --steps 1 --warmup 1 --no-extras --cpu-baseline-frames 1 > $O/bench_C5_$R.json 2>> $O/bench_err.log
 timeout 120 python tools/visit_stats.py C1,C2,C3,C4,C5 2 > $O/visits_$R.txt 2>&1
 timeout 120 python tools/k4_bench.py > $O/k4_$R.txt 2>&1
 timeout 300 python tools/stage_bench.py C1,C2,C3,C4,C5 64 > $O/stages_$R.txt 2>&1

@@ -115,7 +115,7 @@ if os.path.exists(src):
         for k in sorted(tot, key=lambda k: -tot[k]):
             f.write("%-50s %6d %12.2f %10.1f %6.1f%%\n" % (k, cnt[k], tot[k], 1e3 * tot[k] / cnt[k], 100 * tot[k] / all_ms))
 
-for name in ("bench_C1_%s.json" % R, "bench_C3_%s.json" % R, "bench_C4_%s.json" % R, "bench_C5_%s.json" % R, "visits_%s.txt" % R, "bench_%s.json" % R, "bench_ref_%s.json" % R, "k4_%s.txt" % R, "stages_%s.txt" % R, "pytest_gpu_%s.log" % R):
+for name in ("bench_C2_%s.json" % R, "bench_C1_%s.json" % R, "bench_C3_%s.json" % R, "bench_C4_%s.json" % R, "bench_C5_%s.json" % R, "visits_%s.txt" % R, "bench_%s.json" % R, "bench_ref_%s.json" % R, "k4_%s.txt" % R, "stages_%s.txt" % R, "pytest_gpu_%s.log" % R):
     if os.path.exists(os.path.join(G, name)):
         shutil.copy(os.path.join(G, name), os.path.join(P, name))
 print(open(os.path.join(P, "traffic.json")).read())
