@@ -221,6 +221,45 @@ def quick_config(cfg_name, frames, device):
             "stage_ms": {k: v[0] for k, v in st.items()}}
 
 
+def tol_numbers(cfg_name, frames, device):
+    """The OPT-IN tolerance mode (WGPT_MODE_FAST_TOL: shading on fast arithmetic, intersections / camera / RNG pinned) on the
+    bench configuration: rate of the same job, and on one full-size frame against the bit-exact mode: primary ids equal,
+    fraction of samples outside 1e-4 relative, max relative error on the paths whose signature (draws + hit sequence) is
+    equal.  The bit-exact mode stays the headline; tests/test_gpu_tol.py holds the asserts."""
+    import bench_scenes
+    from webgpu_path_tracer_b200 import PathTracer, MODE_FAST, MODE_FAST_TOL
+    scene, cam, W, H, kw = bench_scenes.build(cfg_name)
+    out, probes = {}, {}
+    for name, mode in (("fast", MODE_FAST), ("tol", MODE_FAST_TOL)):
+        pt = PathTracer(W, H, mode=mode, device=device, **kw)
+        pt.write_scene(scene.buffers())
+        pt.write_uniforms(2, 0, cam.viewMatrix)
+        pt.probe_rng(fetch=False)
+        rad, ty, ix, t = pt.probe()
+        probes[name] = (rad, ty, ix, t, pt.probe_rng())
+        if name == "tol":
+            pt.write_uniforms(1, 0, cam.viewMatrix)
+            pt.render(1, min(frames, 16))
+            pt.write_buffer(3, np.zeros(W * H * 4, np.float32))
+            pt.render(1, frames)
+            ms, _n = pt.last_timing()
+            out["Msamples_per_s"] = W * H * kw.get("num_samples", 1) * frames / ms / 1e3
+            out["frames"] = frames
+        pt.close()
+    (rf, tf, xf, df, sf), (rt, tt, xt, dt, st) = probes["fast"], probes["tol"]
+    fin = np.isfinite(rf).all(axis=1) & np.isfinite(rt).all(axis=1)
+    scale = np.maximum(np.abs(np.where(np.isfinite(rf), rf, 0)).max(axis=1), 1e-3)
+    with np.errstate(invalid="ignore"):
+        rel = np.abs(rt.astype(np.float64) - rf).max(axis=1) / scale
+    same = sf == st
+    out.update({"primary_ids_bit_exact": bool(np.array_equal(tf, tt) and np.array_equal(xf, xt) and np.array_equal(df.view(np.uint32), dt.view(np.uint32))),
+                "fraction_outside_1e-4": float(np.where(fin, rel > 1e-4, True).mean()),
+                "fraction_signature_diverged": float((~same).mean()),
+                "max_rel_err_same_signature": float(rel[same & fin].max()) if (same & fin).any() else None,
+                "what": "one full-size frame, tolerance mode vs the bit-exact fast mode (= the oracle, bit for bit)"})
+    return out
+
+
 def per_frame_numbers(device):
     """The reference's own call pattern (renderer.js:163-191): per frame one uniform write, one wgpt_dispatch, one
     present.  (a) strict: dispatch + present every frame (the present waits for the frame: fill + drain of the
@@ -516,7 +555,7 @@ def main():
                "sample": "%d frames of %dx%d (%.1f s of CPU work), extrapolated to the %d-frame job of the GPU step" % (nfr, W, H, dt, job_frames)}
 
     fstats = pt.fast_statistics() if args.mode == "fast" else None
-    other, per_frame = None, None
+    other, per_frame, tol_mode = None, None, None
     if world == 1 and not args.no_extras and args.mode == "fast":
         del l2_flush
         pt.close()
@@ -525,6 +564,7 @@ def main():
             if c != args.config:
                 other[c] = quick_config(c, fr, local_rank)
         per_frame = per_frame_numbers(local_rank)
+        tol_mode = tol_numbers(args.config, min(job_frames, 256), local_rank)
 
     if world > 1:
         par = "%d tile group(s) x %d frame strata, ncclReduce(sum) issued by libwgpt.so on the render stream" % (tw, sw)
@@ -542,7 +582,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
             "gpu_launches": int(launches),
             "roofline": roofline, "cpu_baseline": cpu, "wall_s": wall,
-            "other_configs": other, "per_frame": per_frame, "mgpu_check": mgpu_check,
+            "other_configs": other, "per_frame": per_frame, "tol_mode": tol_mode, "mgpu_check": mgpu_check,
             "rank0_last_render_ms": render_ms,
             "fast_stats": fstats}
     emit(line)

@@ -51,6 +51,14 @@ extern "C" {
 #define WGPT_MODE_FAST  1   /* persistent-thread wavefront over SoA ray queues on the 8-wide quantised
                                BVH; same RNG stream and intersection arithmetic, fast shading math   */
 
+#define WGPT_MODE_FAST_TOL 2 /* OPT-IN tolerance mode: WGPT_MODE_FAST's pipeline with the SHADING of a hit (normal, BSDF
+                               sample, pdfs, throughput) on fast arithmetic -- contracted FMAs, MUFU reciprocals + one
+                               Newton step, f32 libm -- while the camera ray, every intersection and the RNG stream stay
+                               pinned.  Primary hits (type, index, t) remain bit-identical to the reference arithmetic;
+                               per-sample radiance agrees to <= 1e-4 relative except on the paths that diverge (a
+                               discrete decision flips on a last-bit difference: measured 1e-4 .. 1e-3 of the samples,
+                               tests/test_gpu_tol.py, bench.py key `tol_mode`).  NOT bit-comparable with the oracle.  */
+
 /* The WGSL compile-time constants (shaders/header.wgsl:9-13) are run-time parameters here. */
 typedef struct wgpt_config {
     uint32_t struct_size;          /* sizeof(wgpt_config), for forward compatibility */
@@ -130,6 +138,10 @@ int wgpt_present_rgba8_static(wgpt_ctx* ctx, uint8_t* rgba8_out);
  * pixel, the first closest-hit query of the invocation: type 0 sphere / 1 quad / 2 triangle /
  * -1 miss, index (sphere/quad index, Triangle.local_id), t; and pathTrace()'s radiance (3 f32). */
 int wgpt_probe(wgpt_ctx* ctx, float* radiance_out, int32_t* prim_type, int32_t* prim_index, float* prim_t);
+/* Fast modes: path signatures of the last wgpt_probe -- per pixel, the RNG state of the (pixel, frame) item when it finished xor a hash
+ * of its hit sequence (kind and index of every closest hit): equal <=> the path drew the same numbers and hit the same things.  Call once before the probes of interest (out may be NULL)
+ * to switch the recording on.  tests/test_gpu_tol.py uses it to tell diverged paths from non-diverged ones. */
+int wgpt_probe_rng(wgpt_ctx* ctx, uint32_t* out);
 /* Closest hit of caller-supplied rays (6 f32 each: origin, dir); seeds[i] = RNG state on entry. */
 int wgpt_trace_rays(wgpt_ctx* ctx, int n, const float* rays, const uint32_t* seeds,
                     int32_t* prim_type, int32_t* prim_index, float* prim_t);

@@ -10,7 +10,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libwgpt.so")
 
-MODE_EXACT, MODE_FAST = 0, 1
+MODE_EXACT, MODE_FAST, MODE_FAST_TOL = 0, 1, 2
 BINDING_UNIFORMS, BINDING_SPHERES, BINDING_QUADS, BINDING_FRAMEBUFFER = 0, 1, 2, 3
 BINDING_TRIANGLES, BINDING_MESHES, BINDING_TRANSFORMS, BINDING_MATERIALS, BINDING_BVH = 5, 6, 7, 8, 9
 STRIDES = {0: 80, 1: 32, 2: 80, 3: 16, 5: 96, 6: 16, 7: 128, 8: 64, 9: 48}
@@ -20,7 +20,7 @@ EXPORTS = ("wgpt_default_config", "wgpt_create", "wgpt_destroy", "wgpt_last_erro
            "wgpt_read_buffer", "wgpt_device_ptr", "wgpt_dispatch", "wgpt_render", "wgpt_present", "wgpt_probe",
            "wgpt_trace_rays", "wgpt_counters", "wgpt_set_counters", "wgpt_last_timing", "wgpt_synchronize",
            "wgpt_pinned_math", "wgpt_fast_statistics", "wgpt_set_stage_profiling", "wgpt_stage_timings", "wgpt_k4_timing", "wgpt_present_quant_check",
-           "wgpt_timer_mark", "wgpt_timer_elapsed", "wgpt_extend_history", "wgpt_present_rgba8_static", "wgpt_nccl_unique_id", "wgpt_comm_init", "wgpt_reduce_framebuffer", "wgpt_group_create", "wgpt_group_destroy",
+           "wgpt_timer_mark", "wgpt_timer_elapsed", "wgpt_probe_rng", "wgpt_extend_history", "wgpt_present_rgba8_static", "wgpt_nccl_unique_id", "wgpt_comm_init", "wgpt_reduce_framebuffer", "wgpt_group_create", "wgpt_group_destroy",
            "wgpt_group_last_error", "wgpt_group_size", "wgpt_group_ctx", "wgpt_group_write_buffer", "wgpt_group_render",
            "wgpt_group_reduce")
 
@@ -87,6 +87,7 @@ def load_library(path=None):
     L.wgpt_stage_timings.argtypes = [vp, C.POINTER(C.c_float * 4), C.POINTER(C.c_uint64 * 4)]
     L.wgpt_present_rgba8_static.argtypes = [vp, vp]
     L.wgpt_extend_history.argtypes = [vp, vp]
+    L.wgpt_probe_rng.argtypes = [vp, vp]
     L.wgpt_timer_mark.argtypes = [vp, i32]
     L.wgpt_timer_elapsed.argtypes = [vp, C.POINTER(C.c_float)]
     L.wgpt_nccl_unique_id.argtypes = [vp]
@@ -245,6 +246,12 @@ class PathTracer:
         pi, t = np.empty(n, np.int32), np.empty(n, np.float32)
         self._ck(self.L.wgpt_probe(self.h, _p(rad), _p(pt), _p(pi), _p(t)), "wgpt_probe")
         return rad, pt, pi, t
+
+    def probe_rng(self, fetch=True):
+        """Path signatures (final RNG state per pixel) of the last probe(); probe_rng(fetch=False) switches recording on."""
+        out = np.zeros(self.W * self.H, np.uint32) if fetch else None
+        self._ck(self.L.wgpt_probe_rng(self.h, _p(out)), "wgpt_probe_rng")
+        return out
 
     def trace_rays(self, rays, seeds=None):
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)

@@ -116,7 +116,7 @@ int wgpt_create(const wgpt_config* cfg, wgpt_ctx** out) {
     if (cfg->tile_world < 1 || cfg->tile_rank < 0 || cfg->tile_rank >= cfg->tile_world || cfg->tile_rows < 1 ||
         cfg->strata_world < 1 || cfg->strata_rank < 0 || cfg->strata_rank >= cfg->strata_world)
         return set_err(nullptr, WGPT_E_INVALID, "bad shard description");
-    if (cfg->mode != WGPT_MODE_EXACT && cfg->mode != WGPT_MODE_FAST) return set_err(nullptr, WGPT_E_INVALID, "unknown mode");
+    if (cfg->mode != WGPT_MODE_EXACT && cfg->mode != WGPT_MODE_FAST && cfg->mode != WGPT_MODE_FAST_TOL) return set_err(nullptr, WGPT_E_INVALID, "unknown mode");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0)
@@ -168,6 +168,7 @@ void wgpt_destroy(wgpt_ctx* c) {
     if (c->d_ptype) cudaFree(c->d_ptype);
     if (c->d_pindex) cudaFree(c->d_pindex);
     if (c->d_pt) cudaFree(c->d_pt);
+    if (c->d_prng) cudaFree(c->d_prng);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->tm_ev[0]) cudaEventDestroy(c->tm_ev[0]);

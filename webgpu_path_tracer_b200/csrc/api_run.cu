@@ -63,7 +63,7 @@ int wgpt_dispatch(wgpt_ctx* c, uint32_t workgroups) {
     const uint32_t limit = inv > 0xffffffffull ? 0xffffffffu : (uint32_t)inv;
     cudaEventRecord(c->ev0, c->stream);
     c->last_launches = 0;
-    if (c->cfg.mode == WGPT_MODE_FAST && c->cfg.max_bounces >= 1 && limit >= (uint32_t)c->cfg.width * c->cfg.height) {
+    if (c->cfg.mode != WGPT_MODE_EXACT && c->cfg.max_bounces >= 1 && limit >= (uint32_t)c->cfg.width * c->cfg.height) {
         // the frame joins the living wavefront and the call returns (strata belong to wgpt_render: a dispatch is
         // one whole frame in both modes)
         rc = fast_dispatch(c, (int)c->uniforms.frameNum, c->uniforms.resetBuffer != 0.0f);
@@ -88,7 +88,7 @@ int wgpt_render(wgpt_ctx* c, int first_frame, int n_frames) {
     c->uniforms.resetBuffer = 0.0f;
     cudaEventRecord(c->ev0, c->stream);
     c->last_launches = 0;
-    if (c->cfg.mode == WGPT_MODE_FAST && c->cfg.max_bounces >= 1) rc = fast_render(c, first_frame, n_frames, 0);
+    if (c->cfg.mode != WGPT_MODE_EXACT && c->cfg.max_bounces >= 1) rc = fast_render(c, first_frame, n_frames, 0);
     else { rc = fast_close(c); if (!rc) rc = exact_render(c, first_frame, n_frames, 0xffffffffu); }
     if (n_frames > 0) c->uniforms.frameNum = (float)(first_frame + n_frames - 1);
     cudaEventRecord(c->ev1, c->stream);
@@ -127,7 +127,7 @@ int wgpt_probe(wgpt_ctx* c, float* radiance_out, int32_t* prim_type, int32_t* pr
     cudaMemsetAsync(c->d_ptype, 0xff, npix * 4, c->stream);
     cudaMemsetAsync(c->d_pindex, 0xff, npix * 4, c->stream);
     cudaMemsetAsync(c->d_pt, 0, npix * 4, c->stream);
-    if (c->cfg.mode == WGPT_MODE_FAST && c->cfg.max_bounces >= 1) {
+    if (c->cfg.mode != WGPT_MODE_EXACT && c->cfg.max_bounces >= 1) {
         // through the wavefront: render the frame into a scratch copy of binding 3 (reset semantics:
         // the scratch then holds exactly this frame's per-pixel radiance), binding 3 itself untouched
         HostScratch d_fb;
@@ -156,6 +156,23 @@ int wgpt_probe(wgpt_ctx* c, float* radiance_out, int32_t* prim_type, int32_t* pr
     return cuda_err(c, cudaStreamSynchronize(c->stream), "probe");
 }
 
+// Path signatures of the last wgpt_probe in a fast mode: the RNG state of every pixel's item when it finished.  The first
+// call (out == NULL allowed) switches the recording on for the following probes.
+int wgpt_probe_rng(wgpt_ctx* c, uint32_t* out) {
+    if (!c) return WGPT_E_INVALID;
+    if (c->cfg.mode == WGPT_MODE_EXACT) return set_err(c, WGPT_E_STATE, "wgpt_probe_rng: fast modes only");
+    cudaSetDevice(c->cfg.device);
+    const size_t npix = (size_t)c->cfg.width * c->cfg.height;
+    if (!c->d_prng) {
+        cudaError_t e = cudaMalloc((void**)&c->d_prng, npix * 4);
+        if (e != cudaSuccess) return cuda_err(c, e, "probe_rng");
+        cudaMemsetAsync(c->d_prng, 0, npix * 4, c->stream);
+    }
+    if (!out) return WGPT_OK;
+    cudaMemcpyAsync(out, c->d_prng, npix * 4, cudaMemcpyDeviceToHost, c->stream);
+    return cuda_err(c, cudaStreamSynchronize(c->stream), "probe_rng");
+}
+
 int wgpt_trace_rays(wgpt_ctx* c, int n, const float* rays, const uint32_t* seeds, int32_t* prim_type,
                     int32_t* prim_index, float* prim_t) {
     if (!c || n < 0 || (n && (!rays || !prim_type || !prim_index || !prim_t))) return WGPT_E_INVALID;
@@ -171,7 +188,7 @@ int wgpt_trace_rays(wgpt_ctx* c, int n, const float* rays, const uint32_t* seeds
     cudaMemcpyAsync(d_rays.p, rays, (size_t)n * 24, cudaMemcpyHostToDevice, c->stream);
     if (seeds) cudaMemcpyAsync(d_seeds.p, seeds, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream);
     else cudaMemsetAsync(d_seeds.p, 0, (size_t)n * 4, c->stream);
-    if (c->cfg.mode == WGPT_MODE_FAST) {
+    if (c->cfg.mode != WGPT_MODE_EXACT) {
         rc = fast_trace_rays(c, n, (const float*)d_rays.p, (const uint32_t*)d_seeds.p, (int*)d_type.p, (int*)d_index.p, (float*)d_t.p);
         if (rc) return rc;
     } else {

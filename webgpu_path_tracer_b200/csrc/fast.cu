@@ -42,6 +42,7 @@ struct FastState {
     uint32_t* h_flag = nullptr;            // pinned: finished flag copies
     cudaEvent_t flag_ev[2] = {nullptr, nullptr};
     uint32_t* d_fallbacks = nullptr;
+    uint32_t* d_path_sig = nullptr;        // per-slot hit-sequence hash, probes with signatures only
     bool pool_ready = false;
     // stage profiling: a ring of event quadruples, folded into the sums whenever it fills up
     std::vector<cudaEvent_t> prof_ev;
@@ -352,7 +353,18 @@ int fast_submit(wgpt_ctx* c, int first_frame, int n_frames, bool strata, int res
         s.P = F->P;
         s.P.frame0 = f0; s.P.frame_stride = world;
         s.P.bvh_depth = c->bvh_depth;
+        s.P.tol = c->cfg.mode == WGPT_MODE_FAST_TOL ? 1 : 0;
         s.P.prim_type = d_ptype; s.P.prim_index = d_pindex; s.P.prim_t = d_pt;
+        s.P.prim_rng = probe ? c->d_prng : nullptr;
+        s.P.path_sig = nullptr;
+        if (s.P.prim_rng) {                                 // signatures requested (wgpt_probe_rng): the per-slot hit-sequence hash
+            if (!F->d_path_sig) {
+                cudaError_t e = cudaMalloc((void**)&F->d_path_sig, (size_t)F->capacity * 4);
+                if (e != cudaSuccess) return cuda_err(c, e, "path signature array");
+            }
+            cudaMemsetAsync(F->d_path_sig, 0, (size_t)F->capacity * 4, c->stream);
+            s.P.path_sig = F->d_path_sig;
+        }
         s.frame0 = f0; s.stride = world; s.frames = my_frames;
         s.uniforms = c->uniforms; s.fb = c->dbuf[3]; s.reset_first = reset_first; s.probe = probe;
         s.counters_on = c->counters_on;
@@ -451,6 +463,7 @@ void fast_destroy(wgpt_ctx* c) {
     if (F->build_scratch) cudaFree(F->build_scratch);
     free_pool(F);
     if (F->d_fallbacks) cudaFree(F->d_fallbacks);
+    if (F->d_path_sig) cudaFree(F->d_path_sig);
     delete F;
     c->fast = nullptr;
 }

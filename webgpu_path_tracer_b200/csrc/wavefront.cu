@@ -399,7 +399,7 @@ __device__ __forceinline__ void start_sample(const DeviceScene& S, uint32_t pixe
 // SPEC: what the launcher knows about the scene, so that code the scene cannot reach is not in the kernel at all
 // (the generic kernel is 170 KB of instructions; 9 % of its issue stalls were instruction fetches): -1 = nothing
 // (everything decided at run time), else bit 0 = binding 1 holds spheres, bit 1 = IMPORTANCE_SAMPLING is on.
-template <bool COUNT, int SPEC, int THREADS>
+template <bool COUNT, int SPEC, int THREADS, bool TOL>
 __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_shade(DeviceScene S, WfParams P) {
     constexpr bool SPH = SPEC < 0 || (SPEC & 1) != 0;
     constexpr int IS = SPEC < 0 ? -1 : ((SPEC >> 1) & 1);
@@ -530,6 +530,9 @@ __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_s
     v3 thr = V3s(1.0f), acc = V3s(0.0f);
     float4 pix = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 
+    // probes only: hash of the path's hit sequence so far (kind, index of every closest hit; a miss too)
+    uint32_t sig = 0;
+    if (P.path_sig && cls <= WF_CLS_MISS) sig = (P.path_sig[slot] ^ ((uint32_t)(hid.x + 1) << 28) ^ (uint32_t)hid.y) * 0x9E3779B1u;
     if (cls == WF_CLS_IDLE) {
         need_work = true;
     } else if (cls <= WF_CLS_MISS) {
@@ -546,15 +549,8 @@ __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_s
             ray.o = V3(o4.x, o4.y, o4.z); ray.d = V3(e1v.x, e1v.y, e1v.z);
             HitLite h; h.t = o4.w; h.uu = xv.z; h.vv = xv.w; h.kind = hid.x; h.index = hid.y; h.mat_id = hid.z;
             if (resolved) { h.t = h4_resolved.x; h.uu = h4_resolved.y; h.vv = h4_resolved.z; h.index = hid.y; }
-            ObjRayCache oc; oc.reset();
-            ShadeState st;
-            st.p = st.n = st.unit_w = st.u = st.v = V3s(0.0f);
-            st.front_face = false; st.skip_pdf = false; st.doSpecular = 0.0f;
-            st.skip_ray.o = st.skip_ray.d = V3s(0.0f);
-            finalize_hit<SPH>(S, ray, h, tn, st);
-            const Material m = S.materials[h.mat_id];
-            bool early;
-            const bool cont = bounce_update<IS>(S, m, (int)bounce, ray, st, rng, n_draws, acc, thr, early);
+            // the shading of the hit: pinned arithmetic, or (WGPT_MODE_FAST_TOL) the same code on fast arithmetic (shade.cuh)
+            const bool cont = shade_bounce<SPH, IS, TOL>(S, h, tn, (int)bounce, ray, rng, n_draws, acc, thr);
             bounce++;
             ended = !cont || (int)bounce >= S.K.MAX_BOUNCES;           // `for (i < MAX_BOUNCES)`
             alive = !ended;
@@ -572,6 +568,7 @@ __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_s
                 // x / 1 is x (HEAD has NUM_SAMPLES = 1): no need to run three IEEE divisions for it
                 const v3 mean = div == 1.0f ? V3(pix.x, pix.y, pix.z) : V3(pix.x, pix.y, pix.z) / div;
                 P.stage[(size_t)ring_slot * npix + pixel] = make_float4(mean.x, mean.y, mean.z, 1.0f);
+                if (P.prim_rng) P.prim_rng[pixel] = rng ^ (sig * 0x85EBCA6Bu);      // path signature: draws made + hits seen
                 atomicAdd(&s_done[ring_slot], 1u);
                 need_work = true;
             }
@@ -629,6 +626,7 @@ __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_s
                         const float frame = (float)(P.frame0 + (int)frame_k * P.frame_stride);
                         rng = pixel_seed(pixel, frame);
                         scnt = 0;
+                        sig = 0;
                         pix = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                         gen = true; gen_pixel = pixel;
                     } else {
@@ -665,6 +663,7 @@ __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_s
         P.pool.s1[slot] = make_float4(acc.y, acc.z, __uint_as_float(rng), __uint_as_float(pix_i));
         P.pool.x[slot] = make_float4(__uint_as_float(wf_tag(hit_a ? h.kind : (int)HIT_NONE, ncls, h.mat_id)), __int_as_float(h.index), 0.0f, 0.0f);
         if (store_pix) P.pool.pix[slot] = pix;
+        if (P.path_sig) P.path_sig[slot] = sig;
         if (!trace && P.prim_type && (ctr & WF_CTR_FIRST_QUERY_MASK) == 0u) write_probe(S, P, pix_i, hit_a, h);
     } else if (cls <= WF_CLS_IDLE && new_cls != cls) {
         reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = wf_tag(HIT_NONE, new_cls, -1);    // idle (waiting for the window) or dead (no work left)
@@ -779,13 +778,16 @@ int wf_launch_iteration(const DeviceScene& S, const WideBvh& WB, const WfParams&
     const int spec = (S.NUM_SPHERES > 0 ? 1 : 0) | (S.K.IMPORTANCE_SAMPLING ? 2 : 0);
     const unsigned st = P.shade_threads;
     const unsigned shade_blocks = (P.pool.capacity + st - 1u) / st + WF_FRONT_BLOCKS;
-    if (S.counters) k_wf_shade<true, -1, 256><<<shade_blocks, 256, 0, stream>>>(S, P);
+#define WF_SHADE_LAUNCH(C, SP, TH) do { if (P.tol) k_wf_shade<C, SP, TH, true><<<shade_blocks, TH, 0, stream>>>(S, P); \
+                                        else k_wf_shade<C, SP, TH, false><<<shade_blocks, TH, 0, stream>>>(S, P); } while (0)
+    if (S.counters) WF_SHADE_LAUNCH(true, -1, 256);
     else switch (spec) {
-        case 0: k_wf_shade<false, 0, 256><<<shade_blocks, 256, 0, stream>>>(S, P); break;
-        case 1: k_wf_shade<false, 1, WF_SHADE_THREADS_MIXED><<<shade_blocks, WF_SHADE_THREADS_MIXED, 0, stream>>>(S, P); break;
-        case 2: k_wf_shade<false, 2, WF_SHADE_THREADS_MIXED><<<shade_blocks, WF_SHADE_THREADS_MIXED, 0, stream>>>(S, P); break;
-        default: k_wf_shade<false, 3, WF_SHADE_THREADS_MIXED><<<shade_blocks, WF_SHADE_THREADS_MIXED, 0, stream>>>(S, P); break;
+        case 0: WF_SHADE_LAUNCH(false, 0, 256); break;
+        case 1: WF_SHADE_LAUNCH(false, 1, WF_SHADE_THREADS_MIXED); break;
+        case 2: WF_SHADE_LAUNCH(false, 2, WF_SHADE_THREADS_MIXED); break;
+        default: WF_SHADE_LAUNCH(false, 3, WF_SHADE_THREADS_MIXED); break;
     }
+#undef WF_SHADE_LAUNCH
     if (ev) cudaEventRecord(ev[2], stream);
     k_wf_ctl_end<<<1, 32, 0, stream>>>(P);
     if (do_acc) {      // a whole-image launch even when no frame is ready: only every few iterations (fast.cu WF_ACC_EVERY)

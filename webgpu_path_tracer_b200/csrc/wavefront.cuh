@@ -129,9 +129,13 @@ struct WfParams {
     // C3 -9 %); single-material scenes gain nothing from the sort and pay the heavier block (C4 +11 %), so they keep 256.
     // The extend stage marks tie / overflow slots per shade block, so it needs the same number.
     uint32_t shade_threads;
+    int tol;                           // WGPT_MODE_FAST_TOL: shading of a hit on fast arithmetic (shade.cuh wg::tol); intersections, camera, RNG stay pinned
     int do_acc;                        // the accumulate pass is launched right after this iteration's control step (set per launch)
     // optional probe outputs (first closest-hit query of every pixel), indexed by pixel
     int* prim_type; int* prim_index; float* prim_t;
+    uint32_t* path_sig;                // optional, per SLOT: hash of the hit sequence of the path in the slot (probes with signatures only)
+    uint32_t* prim_rng;                // optional: path signature of every (pixel, frame) item when it FINISHED: its RNG state (the draws it
+                                       // made) xor the hash of its hit sequence; indexed by pixel
 };
 
 
