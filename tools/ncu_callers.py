@@ -8,7 +8,7 @@ rep, ksub = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 50
 HELPERS = ("pvec.cuh", "wgpt_pinned_math.h", "intrinsics.hpp", "cuda_fp16.hpp", "device_atomic_functions.hpp", "math_functions.hpp", "device_functions.hpp")
 tmp = tempfile.mkdtemp()
-lib = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "webgpu_path_tracer_b200", "libwgpt.so")
+lib = os.environ.get("WGPT_LIB") or os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "webgpu_path_tracer_b200", "libwgpt.so")
 subprocess.run(["cuobjdump", "-xelf", "all", lib], cwd=tmp, capture_output=True)
 lines = {}
 for cb in glob.glob(os.path.join(tmp, "*.cubin")):

@@ -5,7 +5,7 @@ usage: ncu_lines.py report.ncu-rep kernel_mangled_substring [cubin_substring]"""
 import csv, io, re, subprocess, sys, glob, os, collections, tempfile
 rep, ksub = sys.argv[1], sys.argv[2]
 tmp = tempfile.mkdtemp()
-lib = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "webgpu_path_tracer_b200", "libwgpt.so")
+lib = os.environ.get("WGPT_LIB") or os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "webgpu_path_tracer_b200", "libwgpt.so")
 subprocess.run(["cuobjdump", "-xelf", "all", lib], cwd=tmp, capture_output=True)
 lines = {}
 for cb in glob.glob(os.path.join(tmp, "*.cubin")):
