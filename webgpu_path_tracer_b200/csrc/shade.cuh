@@ -87,7 +87,8 @@ __device__ __forceinline__ wg::v3 to_pinned(v3 a) { return wg::V3(a.x, a.y, a.z)
 template <bool SPH, int IS, bool TOL>
 __device__ __forceinline__ bool shade_bounce(const DeviceScene& S, const HitLite& h, const TriNormals& tn, int bounce, Ray& ray,
                                              uint32_t& rng, unsigned& n_draws, v3& acc, v3& thr) {
-    const Material m = S.materials[h.mat_id];
+    // (the material is loaded AFTER finalize_hit in both flavours: loading it first costs registers across the normal
+    //  computation -- measured, shade +1 %)
     bool early;
     if (TOL) {
         tol::Ray r; r.o = tol::from_pinned(ray.o); r.d = tol::from_pinned(ray.d);
@@ -97,6 +98,7 @@ __device__ __forceinline__ bool shade_bounce(const DeviceScene& S, const HitLite
         st.skip_ray.o = st.skip_ray.d = tol::V3s(0.0f);
         tol::TriNormals t2; t2.a = tn.a; t2.b = tn.b; t2.c = tn.c;
         tol::finalize_hit<SPH>(S, r, h, t2, st);
+        const Material m = S.materials[h.mat_id];
         tol::v3 a = tol::from_pinned(acc), t = tol::from_pinned(thr);
         const bool cont = tol::bounce_update<IS>(S, m, bounce, r, st, rng, n_draws, a, t, early);
         acc = tol::to_pinned(a); thr = tol::to_pinned(t);
@@ -108,6 +110,7 @@ __device__ __forceinline__ bool shade_bounce(const DeviceScene& S, const HitLite
     st.front_face = false; st.skip_pdf = false; st.doSpecular = 0.0f;
     st.skip_ray.o = st.skip_ray.d = V3s(0.0f);
     finalize_hit<SPH>(S, ray, h, tn, st);
+    const Material m = S.materials[h.mat_id];
     return bounce_update<IS>(S, m, bounce, ray, st, rng, n_draws, acc, thr, early);
 }
 

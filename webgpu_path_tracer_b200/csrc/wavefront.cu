@@ -530,9 +530,9 @@ __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_s
     v3 thr = V3s(1.0f), acc = V3s(0.0f);
     float4 pix = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 
-    // probes only: hash of the path's hit sequence so far (kind, index of every closest hit; a miss too)
-    uint32_t sig = 0;
-    if (P.path_sig && cls <= WF_CLS_MISS) sig = (P.path_sig[slot] ^ ((uint32_t)(hid.x + 1) << 28) ^ (uint32_t)hid.y) * 0x9E3779B1u;
+    // probes only: hash of the path's hit sequence so far (kind, index of every closest hit; a miss too).  Kept in its
+    // per-slot array, not in a register: a value live across the whole kernel cost 0.5 % of shade with no probe running.
+    if (P.path_sig && cls <= WF_CLS_MISS) P.path_sig[slot] = (P.path_sig[slot] ^ ((uint32_t)(hid.x + 1) << 28) ^ (uint32_t)hid.y) * 0x9E3779B1u;
     if (cls == WF_CLS_IDLE) {
         need_work = true;
     } else if (cls <= WF_CLS_MISS) {
@@ -568,7 +568,10 @@ __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_s
                 // x / 1 is x (HEAD has NUM_SAMPLES = 1): no need to run three IEEE divisions for it
                 const v3 mean = div == 1.0f ? V3(pix.x, pix.y, pix.z) : V3(pix.x, pix.y, pix.z) / div;
                 P.stage[(size_t)ring_slot * npix + pixel] = make_float4(mean.x, mean.y, mean.z, 1.0f);
-                if (P.prim_rng) P.prim_rng[pixel] = rng ^ (sig * 0x85EBCA6Bu);      // path signature: draws made + hits seen
+                if (P.prim_rng) {                                              // path signature: draws made + hits seen
+                    P.prim_rng[pixel] = rng ^ ((P.path_sig ? P.path_sig[slot] : 0u) * 0x85EBCA6Bu);
+                    if (P.path_sig) P.path_sig[slot] = 0u;                 // the slot's next path starts a new hash
+                }
                 atomicAdd(&s_done[ring_slot], 1u);
                 need_work = true;
             }
@@ -626,7 +629,6 @@ __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_s
                         const float frame = (float)(P.frame0 + (int)frame_k * P.frame_stride);
                         rng = pixel_seed(pixel, frame);
                         scnt = 0;
-                        sig = 0;
                         pix = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                         gen = true; gen_pixel = pixel;
                     } else {
@@ -663,7 +665,6 @@ __global__ void __launch_bounds__(THREADS, WF_SHADE_MINB * 256 / THREADS) k_wf_s
         P.pool.s1[slot] = make_float4(acc.y, acc.z, __uint_as_float(rng), __uint_as_float(pix_i));
         P.pool.x[slot] = make_float4(__uint_as_float(wf_tag(hit_a ? h.kind : (int)HIT_NONE, ncls, h.mat_id)), __int_as_float(h.index), 0.0f, 0.0f);
         if (store_pix) P.pool.pix[slot] = pix;
-        if (P.path_sig) P.path_sig[slot] = sig;
         if (!trace && P.prim_type && (ctr & WF_CTR_FIRST_QUERY_MASK) == 0u) write_probe(S, P, pix_i, hit_a, h);
     } else if (cls <= WF_CLS_IDLE && new_cls != cls) {
         reinterpret_cast<uint32_t*>(&P.pool.x[slot])[0] = wf_tag(HIT_NONE, new_cls, -1);    // idle (waiting for the window) or dead (no work left)
