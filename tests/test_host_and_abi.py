@@ -213,3 +213,23 @@ def test_pfm_round_trip(tmp_path):
     imageio.write_pfm(p, img)
     assert p.read_bytes().startswith(b"PF\n7 5\n-1.0\n")
     assert np.array_equal(imageio.read_pfm(p), img[:, :, :3])
+
+
+def test_shard_grid_assignment_covers_the_job_exactly_once():
+    """tile x strata grid (sharding.shard_of_rank, the rule wgpt_group_create uses): over all ranks every (pixel, frame)
+    of a job is rendered exactly once, for every split bench.py uses."""
+    from webgpu_path_tracer_b200 import sharding
+    W, H, first, n = 40, 37, 3, 11
+    for world in (1, 2, 4, 8):
+        for tiles in sorted({1, sharding.default_tile_groups(world), world}):
+            count = np.zeros((n, H * W), np.int32)
+            for rank in range(world):
+                tr, tw, sr, sw = sharding.shard_of_rank(rank, world, tiles)
+                assert (tw, sw) == (tiles, world // tiles)
+                mask = sharding.tile_mask(W, H, tr, tw, 8)
+                for f in sharding.strata_frames(first, n, sr, sw):
+                    count[f - first] += mask
+            assert (count == 1).all(), (world, tiles)
+    assert [sharding.default_tile_groups(w) for w in (1, 2, 4, 8)] == [1, 1, 2, 4]
+    with pytest.raises(ValueError):
+        sharding.shard_of_rank(0, 6, 4)
