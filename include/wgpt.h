@@ -125,7 +125,7 @@ int wgpt_present(wgpt_ctx* ctx, float* rgba_out, uint8_t* rgba8_out);
 /* Bytes-only present that ALLOCATES NOTHING.  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
  * forbid it).  Same kernel and the same bytes as wgpt_present(ctx, NULL, rgba8_out) -- wgpt_present cudaMallocs its
- * device staging on every call -- but the RGBA8 image is staged in a static device array of
+ * device staging on a context's first call -- but the RGBA8 image is staged in a static device array of
  * WGPT_STATIC_PRESENT_MAX_PIXELS x 4 bytes (8 MiB) that every GPU that loads the library holds until exit.  Images with
  * more pixels are rejected with WGPT_E_INVALID.  Every call on a device shares that array (it keeps the last call's
  * bytes; each call overwrites what it reads back), so calls that OVERLAP on the GPU -- two contexts of one device, two

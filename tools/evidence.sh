@@ -15,6 +15,7 @@ for cfg in C4 C2; do
 done
 python tools/evidence_collect.py $R --traffic-only > $O/traffic_collect.log 2>&1; echo "traffic rc=$?"; cp profiles/traffic.json $O/traffic.json
 timeout 900 python bench.py --steps 3 --warmup 3 > $O/bench_$R.json 2> $O/bench_err.log; echo "bench rc=$?"
+[ -n "$LITE" ] && { ls -la $O | tail -30; exit 0; }   # LITE=1: tests, captures, traffic stamp and the default bench only (a host-side change)
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref_$R.json 2>> $O/bench_err.log; echo "bench ref rc=$?"
 timeout 200 python bench.py --config C1 --steps 5 --warmup 3 --no-extras --cpu-baseline-frames 8 > $O/bench_C1_$R.json 2>> $O/bench_err.log
 timeout 200 python bench.py --config C2 --steps 5 --warmup 3 --no-extras --cpu-baseline-frames 8 > $O/bench_C2_$R.json 2>> $O/bench_err.log

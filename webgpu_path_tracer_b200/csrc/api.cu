@@ -169,6 +169,7 @@ void wgpt_destroy(wgpt_ctx* c) {
     if (c->d_pindex) cudaFree(c->d_pindex);
     if (c->d_pt) cudaFree(c->d_pt);
     if (c->d_prng) cudaFree(c->d_prng);
+    for (void* q : c->d_present) if (q) cudaFree(q);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->tm_ev[0]) cudaEventDestroy(c->tm_ev[0]);

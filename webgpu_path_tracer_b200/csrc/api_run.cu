@@ -105,15 +105,17 @@ int wgpt_present(wgpt_ctx* c, float* rgba_out, uint8_t* rgba8_out) {
         if (rc) return rc;
     }
     const uint32_t npix = (uint32_t)c->cfg.width * c->cfg.height;
-    HostScratch d_rgba, d_rgba8;
+    // device staging lives in the context (the image size is fixed at wgpt_create): the per-frame loop of
+    // renderer.js:172-184 calls this every frame, and a cudaMalloc / cudaFree pair per call cost ~3 ms of its 9
     cudaError_t e;
-    if (rgba_out && (e = cudaMalloc(&d_rgba.p, (size_t)npix * 16)) != cudaSuccess) return cuda_err(c, e, "present");
-    if (rgba8_out && (e = cudaMalloc(&d_rgba8.p, (size_t)npix * 4)) != cudaSuccess) return cuda_err(c, e, "present");
+    if (rgba_out && !c->d_present[0] && (e = cudaMalloc(&c->d_present[0], (size_t)npix * 16)) != cudaSuccess) return cuda_err(c, e, "present");
+    if (rgba8_out && !c->d_present[1] && (e = cudaMalloc(&c->d_present[1], (size_t)npix * 4)) != cudaSuccess) return cuda_err(c, e, "present");
+    float4* d_rgba = rgba_out ? (float4*)c->d_present[0] : nullptr;
+    uchar4* d_rgba8 = rgba8_out ? (uchar4*)c->d_present[1] : nullptr;
     const int clear = c->uniforms.resetBuffer == 1.0f;
-    launch_present((const float4*)c->dbuf[3], (float4*)c->dbuf[3], (float4*)d_rgba.p, (uchar4*)d_rgba8.p, npix,
-                   c->uniforms.frameNum, clear, c->stream);
-    if (rgba_out) cudaMemcpyAsync(rgba_out, d_rgba.p, (size_t)npix * 16, cudaMemcpyDeviceToHost, c->stream);
-    if (rgba8_out) cudaMemcpyAsync(rgba8_out, d_rgba8.p, (size_t)npix * 4, cudaMemcpyDeviceToHost, c->stream);
+    launch_present((const float4*)c->dbuf[3], (float4*)c->dbuf[3], d_rgba, d_rgba8, npix, c->uniforms.frameNum, clear, c->stream);
+    if (rgba_out) cudaMemcpyAsync(rgba_out, d_rgba, (size_t)npix * 16, cudaMemcpyDeviceToHost, c->stream);
+    if (rgba8_out) cudaMemcpyAsync(rgba8_out, d_rgba8, (size_t)npix * 4, cudaMemcpyDeviceToHost, c->stream);
     return cuda_err(c, cudaStreamSynchronize(c->stream), "present");
 }
 

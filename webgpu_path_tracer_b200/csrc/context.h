@@ -28,6 +28,7 @@ struct wgpt_ctx {
     uint32_t shard_pixels = 0;
     // probe scratch
     float* d_radiance = nullptr; int* d_ptype = nullptr; int* d_pindex = nullptr; float* d_pt = nullptr;
+    void* d_present[2] = {nullptr, nullptr};    // wgpt_present's device staging (f32 image, RGBA8 image): kept between calls
     uint32_t* d_prng = nullptr;            // final RNG state per pixel of the last fast-mode probe (allocated by wgpt_probe_rng_enable)
     wg::FastState* fast = nullptr;         // wide BVH + wavefront pool (fast.cu)
     bool wide_dirty = true;

@@ -151,7 +151,7 @@ void launch_accumulate(float4* fb, const float4* frame, uint32_t npix, int reset
 // ---------------------------------------------------------------------------------------------------------------
 // wgpt_present_rgba8_static -- the bytes-only present WITHOUT any allocation (no counterpart in the reference; added
 // for callers that cannot call cudaMalloc: code under CUDA graph capture, tight
-// serving loops, harnesses that forbid it).  wgpt_present cudaMallocs its device staging on every call; this variant
+// serving loops, harnesses that forbid it).  wgpt_present cudaMallocs its device staging on a context's first call; this variant never allocates: it
 // stages the RGBA8 image in a file-scope device array of WGPT_STATIC_PRESENT_MAX_PIXELS x 4 bytes (8 MiB), which every
 // GPU that loads the library holds until exit.
 //   * In HOST code the array's name is a host-side stand-in, not a device address: its device address is looked up once
